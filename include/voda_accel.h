@@ -1,0 +1,220 @@
+/*
+ * voda_accel.h — C ABI of the B200 engine for Voda's allocation + placement hot path.
+ *
+ * Every entry point is a plain `extern "C"` function over pointers and sizes (no torch or
+ * C++ types), so the reference's Go services can bind it through cgo (INTEGRATION.md shows
+ * the shim).  Each declaration cites the reference interface it stands in for; paths are
+ * relative to the reference tree (heyfey/vodascheduler).
+ *
+ * Conventions
+ *   - The caller owns every buffer.  `voda_*` (no suffix) entry points take HOST pointers
+ *     and do the host<->device copies themselves (pinned memory from voda_host_alloc makes
+ *     those copies asynchronous); `voda_*_dev` entry points take DEVICE pointers and only
+ *     enqueue kernels on the context's stream.
+ *   - Return value = infrastructure outcome (VODA_OK or a negative VODA_E_*; text from
+ *     voda_last_error).  Per-round reference outcome goes to out_status[round]
+ *     (VODA_ST_*): the reference reports failure by panicking (pkg/algorithm/utils.go:29-40,
+ *     ffdl_optimizer.go:109-114), and voda_status_str() returns the same message text.
+ *   - A voda_ctx owns one device, its streams and its scratch memory.  It is NOT thread
+ *     safe: use one context per goroutine / OS thread.  There is no global mutable state.
+ *   - There is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef VODA_ACCEL_H
+#define VODA_ACCEL_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- infrastructure return codes -------------------------------------------------- */
+#define VODA_OK             0
+#define VODA_E_INVALID     -1   /* bad argument (NULL array the policy needs, negative size ...) */
+#define VODA_E_CUDA        -2   /* a CUDA runtime call failed; see voda_last_error            */
+#define VODA_E_NOMEM       -3   /* scratch / staging allocation failed                         */
+#define VODA_E_UNSUPPORTED -4   /* shape outside what the kernels handle       */
+#define VODA_E_TOO_LARGE   -5   /* request exceeds a fixed capacity (no-allocation entry point)*/
+
+/* ---- per-round status: the reference's panic messages ------------------------------ */
+#define VODA_ST_OK              0
+#define VODA_ST_NEGATIVE        1  /* "Invalid GPU allocations: can't be negative"      utils.go:29-31 */
+#define VODA_ST_LESS_THAN_MIN   2  /* "Invalid GPU allocations: less than job min gpu"  utils.go:32-34 */
+#define VODA_ST_EXCEEDED_MAX    3  /* "Invalid GPU allocations: exceeded job max gpu"   utils.go:35-37 */
+#define VODA_ST_EXCEEDED_TOTAL  4  /* "Invalid GPU allocations: exceeded total GPUs"    utils.go:40-42 */
+#define VODA_ST_INFEASIBLE      5  /* "infeasible"                              ffdl_optimizer.go:109-114 */
+#define VODA_ST_NOT_FOUND       6  /* "Not found"                  types.go:45, elastic_tiresias.go:188-189 */
+#define VODA_ST_NONTERMINATING  7  /* guard: the reference loop would never end (bestFit, placement_manager.go:437-485) */
+#define VODA_ST_BOUND           8  /* round exceeds the max_jobs / max_total_gpu the caller declared */
+#define VODA_ST_RUNTIME_PANIC   9  /* the Go runtime itself would panic (makeslice with negative total) */
+
+/* ---- policies: the eight names of NewAlgorithmFactory, pkg/algorithm/types.go:26-47 - */
+#define VODA_ALGO_FIFO             0
+#define VODA_ALGO_ELASTIC_FIFO     1
+#define VODA_ALGO_SRJF             2
+#define VODA_ALGO_ELASTIC_SRJF     3
+#define VODA_ALGO_TIRESIAS         4
+#define VODA_ALGO_ELASTIC_TIRESIAS 5
+#define VODA_ALGO_FFDL_OPTIMIZER   6
+#define VODA_ALGO_AFSL             7
+#define VODA_ALGO_COUNT            8
+
+typedef struct voda_ctx voda_ctx;
+
+/* Create / destroy a context bound to CUDA device `device`.  Fails (VODA_E_CUDA) when no
+ * device is present — there is no CPU path behind this library. */
+int  voda_ctx_create(int device, voda_ctx** out);
+void voda_ctx_destroy(voda_ctx* ctx);
+/* The cudaStream_t (as void*) that *_dev entry points launch on; time with events on it. */
+void* voda_ctx_stream(voda_ctx* ctx);
+/* Block until everything enqueued on the context has finished. */
+int  voda_ctx_sync(voda_ctx* ctx);
+/* Number of kernels of this library launched through the context since it was created. */
+int64_t voda_ctx_launch_count(voda_ctx* ctx);
+const char* voda_last_error(voda_ctx* ctx);
+const char* voda_status_str(int32_t status);
+const char* voda_version(void);
+
+/* Name <-> id of a policy.  Replaces the string switch of NewAlgorithmFactory
+ * (pkg/algorithm/types.go:26-47): unknown name -> -1 (the reference returns
+ * errors.New("Not found")).  voda_algo_need_job_info mirrors NeedJobInfo()
+ * (srjf.go:58-60, elastic_srjf.go:78-80, elastic_tiresias.go:165-167,
+ * ffdl_optimizer.go:136-138, afsl.go:68-70; false for the others). */
+int         voda_algo_from_name(const char* name);
+const char* voda_algo_name(int32_t algo);
+int         voda_algo_need_job_info(int32_t algo);
+
+/* Page-locked host memory for the host-pointer entry points (optional but recommended). */
+void* voda_host_alloc(size_t bytes);
+void  voda_host_free(void* p);
+
+/*
+ * A batch of R independent scheduling rounds, struct-of-arrays.  Round r owns jobs
+ * [job_off[r], job_off[r+1]) in the INPUT order of the slice handed to Schedule() — input
+ * order is part of the input because every sort in the reference is stable.
+ * Field sources: pkg/common/trainingjob/trainingjob.go:17-66.
+ *   submit_*     TrainingJob.SubmitTime            (Time.Before == lexicographic (sec, nsec))
+ *   first_*      TrainingJob.Metrics.FirstStartTime
+ *   priority     TrainingJob.Priority
+ *   num/min/max  TrainingJob.Config.{NumProc,MinNumProc,MaxNumProc}
+ *   remaining    TrainingJob.Info.EstimatedRemainningTimeSec (float32)
+ *   speedup      TrainingJob.Info.Speedup as a dense table: speedup[job*stride + g] is the
+ *                value under key fmt.Sprint(g); a key the map lacks is 0.0f, and so is every
+ *                g outside [0, stride).
+ * Arrays a policy never reads may be NULL ("inputs per policy").
+ */
+typedef struct {
+  int32_t        algo;                 /* VODA_ALGO_*                                        */
+  int32_t        rounds;               /* R                                                  */
+  const int32_t* job_off;              /* [R+1] ascending, job_off[0] == 0                   */
+  const int32_t* total_gpu;            /* [R]  second argument of Schedule()                 */
+  const int64_t* submit_sec;           /* [jobs] */
+  const int32_t* submit_nsec;          /* [jobs] */
+  const int64_t* first_sec;            /* [jobs] */
+  const int32_t* first_nsec;           /* [jobs] */
+  const int32_t* priority;             /* [jobs] */
+  const int32_t* num_proc;             /* [jobs] */
+  const int32_t* min_proc;             /* [jobs] */
+  const int32_t* max_proc;             /* [jobs] */
+  const float*   remaining_sec;        /* [jobs] */
+  const float*   speedup;              /* [jobs * speedup_stride] */
+  int32_t        speedup_stride;       /* W; the reference's default tables have 34 entries  */
+  int32_t        queue_num;            /* TiresiasQueueNum, tiresias.go:17-24; 0 -> 2        */
+  int32_t        compaction_threshold; /* ElasticTiresiasCompactionThreshold,
+                                          elastic_tiresias.go:18-22; negative -> 10          */
+  int32_t        max_jobs;             /* upper bound of jobs per round; 0 -> computed       */
+  int32_t        max_total_gpu;        /* upper bound of total_gpu;      0 -> computed       */
+} voda_alloc_batch;
+
+/*
+ * Replaces SchedulerAlgorithm.Schedule(ReadyJobs, int) types.JobScheduleResult
+ * (pkg/algorithm/types.go:19-24; call site pkg/allocator/allocator/resource_allocator.go:106)
+ * for a whole batch of rounds.  out_gpus[j] is the reference's result[job.Name] for the job
+ * at flat index j (every input job gets an entry, 0 when unallocated); out_status[r] is
+ * VODA_ST_OK or the panic the reference would raise for round r, in which case out_gpus of
+ * that round holds the allocation the reference had computed when it panicked.
+ */
+int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* host_batch,
+                  int32_t* out_gpus /*[jobs]*/, int32_t* out_status /*[R]*/);
+/* Same, every pointer (inside the struct too) is a device pointer; max_jobs and
+ * max_total_gpu must be given.  Asynchronous on voda_ctx_stream(). */
+int voda_allocate_dev(voda_ctx* ctx, const voda_alloc_batch* dev_batch,
+                      int32_t* d_out_gpus, int32_t* d_out_status);
+
+/*
+ * Replaces m := munkres.NewMatrix(n); m.A = A; munkres.ComputeMunkresMax(m)
+ * (github.com/heyfey/munkres@d4f16a25250d, not vendored; call site
+ * pkg/placement/placement_manager.go:505-512) for `batch` independent n x n matrices.
+ * A is row-major int64, A[b][row*n + col].  out_col_of_row[b][row] is the column of the
+ * RowCol{Row,Col} pair whose Row == row (the reference returns pairs in row order).
+ * 1 <= n <= 128 (one CTA keeps the whole matrix in shared memory).
+ */
+int voda_munkres_max(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t* A,
+                     int32_t* out_col_of_row /*[batch*n]*/, int32_t* out_status /*[batch]*/);
+int voda_munkres_max_dev(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t* d_A,
+                         int32_t* d_out_col_of_row, int32_t* d_out_status);
+
+/*
+ * A batch of R independent placement rounds: the arithmetic core of
+ * PlacementManager.Place (pkg/placement/placement_manager.go:306-332) after releaseSlots,
+ * i.e. bestFit (:415-487) + scoreCandidates/score (:525-544) + ComputeMunkresMax (:505-507)
+ * + the rename of logical nodes (:509-511).  Everything the reference takes from Go map
+ * iteration order is an explicit array here.
+ *   node_off[r]..node_off[r+1]   the round's nodes.  node_slots[i] = totalSlots of LOGICAL
+ *                                node i (order of the list built at :317-320); column c of
+ *                                the score matrix is PHYSICAL node c (order of :494-497).
+ *   req_off / req_workers        the round's requests in jobRequests iteration order;
+ *                                request q of the round is "job q".
+ *   prev_off / prev_job /        current (post-release) contents of the physical nodes, CSR
+ *   prev_workers                 over the flat node index: entries of node i are
+ *                                [prev_off[i], prev_off[i+1]), prev_job is a round-local job
+ *                                index, prev_workers its jobNumWorkers value on that node.
+ */
+typedef struct {
+  int32_t        rounds;
+  const int32_t* node_off;      /* [R+1] */
+  const int32_t* node_slots;    /* [nodes] */
+  const int32_t* req_off;       /* [R+1] */
+  const int32_t* req_workers;   /* [requests] */
+  const int32_t* prev_off;      /* [nodes+1] */
+  const int32_t* prev_job;      /* [prev entries] */
+  const int32_t* prev_workers;  /* [prev entries] */
+  int32_t        max_nodes;     /* upper bound of nodes per round (<= 128); 0 -> computed    */
+  int32_t        max_requests;  /* upper bound of requests per round;       0 -> computed    */
+} voda_place_batch;
+
+/*
+ * Outputs, per round r with n nodes and m requests (entry base e0 = req_off[r] + node_off[r],
+ * entry capacity m + n — bestFit creates at most one entry per request plus one per node):
+ *   out_phys_of_logical[node_off[r] + i]  physical column bound to logical node i (:509-511)
+ *   out_free[node_off[r] + i]             freeSlots of logical node i after bestFit (can be
+ *                                         negative: reference quirk, placement_manager.go:479-482)
+ *   out_lay_cnt[r]                        number of (node, job, workers) entries bestFit made
+ *   out_lay_node/job/workers[e0 + t]      entry t in creation order: logical node index,
+ *                                         round-local job index, jobNumWorkers value
+ *   out_score[r]                          total overlap score of the chosen binding (:512)
+ *   out_cross[r]                          jobs split across nodes (crossNode, :431,476)
+ *   out_status[r]                         VODA_ST_OK / VODA_ST_NONTERMINATING / VODA_ST_BOUND;
+ *                                         the other outputs of a round are unspecified
+ *                                         unless its status is VODA_ST_OK
+ */
+typedef struct {
+  int32_t* phys_of_logical;  /* [nodes] */
+  int32_t* free_slots;       /* [nodes] */
+  int32_t* lay_cnt;          /* [R] */
+  int32_t* lay_node;         /* [requests + nodes] */
+  int32_t* lay_job;          /* [requests + nodes] */
+  int32_t* lay_workers;      /* [requests + nodes] */
+  int64_t* score;            /* [R] */
+  int32_t* cross;            /* [R] */
+  int32_t* status;           /* [R] */
+} voda_place_out;
+
+int voda_place(voda_ctx* ctx, const voda_place_batch* host_batch, const voda_place_out* host_out);
+int voda_place_dev(voda_ctx* ctx, const voda_place_batch* dev_batch, const voda_place_out* dev_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VODA_ACCEL_H */
