@@ -1,0 +1,115 @@
+"""GPU parity of the allocation kernels against the CPU oracle, through the C ABI
+(voda_allocate: host buffers in/out).  Integer outputs: the bar is bit-exact equality of every
+per-job GPU count and every per-round status."""
+import numpy as np
+import pytest
+
+from helpers import batch_from_jobs, load_kats
+from vodascheduler_b200 import ALGO_NAMES, synth
+
+pytestmark = pytest.mark.gpu
+
+KATS = load_kats()
+# policies whose kernels exist; extended as kernels land
+from vodascheduler_b200.supported import SUPPORTED_ALGOS  # noqa: E402
+
+ALGOS = [a for a in ALGO_NAMES if a in SUPPORTED_ALGOS]
+
+
+def _same(ctx, oracle, b, dense=True, threads=8):
+    g_ref, s_ref = oracle.allocate(b, dense=dense, threads=threads)
+    g, s = ctx.allocate(b)
+    bad = np.nonzero(s != s_ref)[0]
+    assert bad.size == 0, f"status differs in rounds {bad[:5]}: gpu {s[bad[:5]]} ref {s_ref[bad[:5]]}"
+    badj = np.nonzero(g != g_ref)[0]
+    assert badj.size == 0, f"{badj.size} job allocations differ, first at {badj[:5]}: gpu {g[badj[:5]]} ref {g_ref[badj[:5]]}"
+    return g, s
+
+
+@pytest.mark.parametrize("kat", [k for k in KATS["alloc"] if k["algo"] in SUPPORTED_ALGOS],
+                         ids=lambda k: f"KAT-{k['kat']}-{k['algo']}")
+def test_kat(ctx, kat):
+    b = batch_from_jobs(kat["algo"], [(kat["jobs"], kat["total"])])
+    g, st = ctx.allocate(b)
+    assert st[0] == kat["status"]
+    if kat["expect"] is not None:
+        assert {j["name"]: int(x) for j, x in zip(kat["jobs"], g)} == kat["expect"]
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_random_vs_faithful_oracle(ctx, oracle, algo):
+    """Small enough for the structure-faithful (string-map) restatement."""
+    b = synth.jobs_batch(algo, rounds=64, jobs_per_round=48, total_gpu=120, ragged=True)
+    _same(ctx, oracle, b, dense=False, threads=4)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_quirks(ctx, oracle, algo):
+    """min == max, min > max, Priority 2, zero totals, flat curves, heavy ties: statuses too."""
+    b = synth.quirk_batch(algo, rounds=600, jobs_per_round=40, total_gpu=64)
+    g, s = _same(ctx, oracle, b)
+    assert (s != 0).any() and (s == 0).any()
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+@pytest.mark.parametrize("jobs,total", [(1, 1), (3, 0), (7, 3), (33, 31), (64, 16), (129, 257), (300, 1000)])
+def test_shapes(ctx, oracle, algo, jobs, total):
+    b = synth.jobs_batch(algo, rounds=24, jobs_per_round=jobs, total_gpu=total)
+    _same(ctx, oracle, b)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_empty_and_ragged(ctx, oracle, algo):
+    b = synth.jobs_batch(algo, rounds=40, jobs_per_round=20, total_gpu=50, ragged=True)
+    # splice in empty rounds
+    off = b.job_off.copy()
+    off[5] = off[4]
+    off = np.maximum.accumulate(off)
+    cnt = np.diff(off)
+    keep = np.concatenate([np.arange(b.job_off[r], b.job_off[r] + cnt[r]) for r in range(b.rounds)]).astype(np.int64)
+    from vodascheduler_b200.batch import _ALLOC_ARRAYS
+    for name, _ in _ALLOC_ARRAYS[2:]:
+        v = getattr(b, name)
+        if name == "speedup":
+            v = v.reshape(-1, b.speedup_stride)[keep].reshape(-1)
+        else:
+            v = v[keep]
+        setattr(b, name, np.ascontiguousarray(v))
+    b.job_off = np.concatenate([[0], np.cumsum(cnt)]).astype(np.int32)
+    _same(ctx, oracle, b)
+    # zero rounds
+    z = synth.jobs_batch(algo, rounds=0, jobs_per_round=4, total_gpu=8)
+    g, s = ctx.allocate(z)
+    assert g.size == 0 and s.size == 0
+
+
+def test_ffdl_full_size_rounds(ctx, oracle):
+    """BASELINE config 2 shape (256 jobs x 1024 GPUs), a sample checked against the oracle."""
+    b = synth.jobs_batch("FfDLOptimizer", rounds=48, jobs_per_round=256, total_gpu=1024)
+    g, s = _same(ctx, oracle, b)
+    assert (s == 0).all()
+    per_round = g.reshape(48, 256).sum(1)
+    assert (per_round <= 1024).all() and (per_round > 900).all()
+
+
+def test_ffdl_wide_max_and_table_edge(ctx, oracle):
+    """max_proc beyond the dense table (map miss => S = 0) and beyond 255 (uint16 SOL path)."""
+    b = synth.jobs_batch("FfDLOptimizer", rounds=12, jobs_per_round=24, total_gpu=700)
+    b.max_proc = (b.max_proc.astype(np.int64) * np.where(np.arange(b.jobs) % 5 == 0, 40, 2)).astype(np.int32)
+    _same(ctx, oracle, b)
+    b.total_gpu[:] = 90
+    _same(ctx, oracle, b)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_chunked_pipeline_equals_single(ctx, oracle, algo):
+    """A batch large enough to be cut into several pipeline chunks gives the same answer."""
+    b = synth.jobs_batch(algo, rounds=3000, jobs_per_round=32, total_gpu=64, ragged=True)
+    _same(ctx, oracle, b)
+
+
+def test_declared_bounds_are_enforced(ctx):
+    b = synth.jobs_batch(ALGOS[0], rounds=4, jobs_per_round=16, total_gpu=32)
+    b.max_jobs = 8
+    g, s = ctx.allocate(b)
+    assert (s == 8).all() and (g == 0).all()

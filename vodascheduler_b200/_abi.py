@@ -1,7 +1,7 @@
 """ctypes mirror of include/voda_accel.h (struct layouts, constants, prototypes).
 
 Pure declarations: nothing here computes.  Shared by the product binding (_lib.py) and by the
-test-only oracle binding (oracle/oracle.py), so both see exactly the same struct layout.
+test-only checker binding kept outside this package, so both see the same struct layout.
 """
 import ctypes as C
 

@@ -1,0 +1,162 @@
+"""ctypes binding of vodascheduler_b200/libvoda_accel.so (the C ABI of include/voda_accel.h).
+
+Fails loudly: a missing library, a missing symbol or a missing CUDA device raises
+EngineError.  There is no fallback path of any kind behind these calls.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _abi
+from .batch import AllocBatch, PlaceBatch, PlaceOut
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libvoda_accel.so")
+
+
+class EngineError(RuntimeError):
+    """Infrastructure failure of the engine (not a per-round reference panic)."""
+
+
+def library_path():
+    return _SO
+
+
+_lib = None
+
+
+def load_library():
+    """dlopen the built CUDA library and bind every symbol the header declares."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            raise EngineError(
+                f"{_SO} is missing: build it with `python -m vodascheduler_b200.build` "
+                "(nvcc, sm_100a).  This package has no CPU fallback.")
+        try:
+            _lib = _abi.bind(C.CDLL(_SO))
+        except (OSError, AttributeError) as e:
+            raise EngineError(f"cannot load {_SO}: {e}") from e
+    return _lib
+
+
+def status_str(code):
+    return load_library().voda_status_str(int(code)).decode()
+
+
+class Context:
+    """voda_ctx: one CUDA device, its streams and scratch.  Not thread safe."""
+
+    def __init__(self, device=0):
+        self._lib = load_library()
+        h = C.c_void_p()
+        rc = self._lib.voda_ctx_create(int(device), C.byref(h))
+        if rc != 0:
+            raise EngineError(f"voda_ctx_create({device}) failed rc={rc}: "
+                              f"{self._lib.voda_last_error(None).decode()}")
+        self._h = h
+        self.device = int(device)
+
+    # -- plumbing ----------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.voda_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise EngineError(f"{what} failed rc={rc}: {self._lib.voda_last_error(self._h).decode()}")
+
+    @property
+    def stream(self):
+        """cudaStream_t (int) the *_dev entry points launch on."""
+        return self._lib.voda_ctx_stream(self._h)
+
+    def sync(self):
+        self._check(self._lib.voda_ctx_sync(self._h), "voda_ctx_sync")
+
+    @property
+    def launches(self):
+        return int(self._lib.voda_ctx_launch_count(self._h))
+
+    # -- allocation --------------------------------------------------------------------
+    def allocate(self, batch: AllocBatch, out_gpus=None, out_status=None):
+        """Host buffers in, host buffers out (H2D, kernels, D2H inside the call)."""
+        if out_gpus is None:
+            out_gpus = np.zeros(max(1, batch.jobs), np.int32)
+        if out_status is None:
+            out_status = np.full(max(1, batch.rounds), -1, np.int32)
+        s = batch.struct()
+        rc = self._lib.voda_allocate(self._h, C.byref(s), out_gpus.ctypes.data, out_status.ctypes.data)
+        self._check(rc, "voda_allocate")
+        return out_gpus[:batch.jobs], out_status[:batch.rounds]
+
+    def allocate_dev(self, dev_batch: AllocBatch, d_out_gpus, d_out_status):
+        """Device-resident batch (torch tensors); asynchronous on self.stream."""
+        s = dev_batch.struct()
+        rc = self._lib.voda_allocate_dev(self._h, C.byref(s), d_out_gpus.data_ptr(), d_out_status.data_ptr())
+        self._check(rc, "voda_allocate_dev")
+
+    # -- munkres -----------------------------------------------------------------------
+    def munkres_max(self, A):
+        A = np.ascontiguousarray(A, dtype=np.int64)
+        if A.ndim == 2:
+            A = A[None]
+        batch, n = A.shape[0], A.shape[1]
+        out = np.full(max(1, batch * n), -1, np.int32)
+        st = np.full(max(1, batch), -1, np.int32)
+        rc = self._lib.voda_munkres_max(self._h, n, batch, A.ctypes.data, out.ctypes.data, st.ctypes.data)
+        self._check(rc, "voda_munkres_max")
+        return out[:batch * n].reshape(batch, n), st[:batch]
+
+    def munkres_max_dev(self, n, batch, d_A, d_out, d_status):
+        rc = self._lib.voda_munkres_max_dev(self._h, n, batch, d_A.data_ptr(), d_out.data_ptr(), d_status.data_ptr())
+        self._check(rc, "voda_munkres_max_dev")
+
+    # -- placement ---------------------------------------------------------------------
+    def place(self, batch: PlaceBatch, out: PlaceOut | None = None) -> PlaceOut:
+        if out is None:
+            out = PlaceOut(batch.rounds, batch.nodes, batch.requests)
+        s, o = batch.struct(), out.struct()
+        self._check(self._lib.voda_place(self._h, C.byref(s), C.byref(o)), "voda_place")
+        return out
+
+    def place_dev(self, dev_batch: PlaceBatch, dev_out_struct):
+        s = dev_batch.struct()
+        self._check(self._lib.voda_place_dev(self._h, C.byref(s), C.byref(dev_out_struct)), "voda_place_dev")
+
+    # -- pinned host memory ------------------------------------------------------------
+    def pinned(self, shape, dtype):
+        """numpy array backed by voda_host_alloc (page-locked) memory."""
+        dtype = np.dtype(dtype)
+        n = int(np.prod(shape))
+        p = self._lib.voda_host_alloc(max(1, n * dtype.itemsize))
+        if not p:
+            raise EngineError("voda_host_alloc failed")
+        buf = (C.c_char * max(1, n * dtype.itemsize)).from_address(p)
+        arr = np.frombuffer(buf, dtype=dtype, count=n).reshape(shape)
+        self._pins = getattr(self, "_pins", [])
+        self._pins.append(p)
+        return arr
+
+    def pin_batch(self, batch: AllocBatch) -> AllocBatch:
+        """Copy of `batch` whose arrays live in page-locked memory."""
+        from .batch import _ALLOC_ARRAYS
+        b = AllocBatch.__new__(AllocBatch)
+        b.__dict__.update(batch.__dict__)
+        for name, dt in _ALLOC_ARRAYS:
+            v = getattr(batch, name)
+            if v is not None:
+                pv = self.pinned(v.shape, dt)
+                pv[...] = v
+                setattr(b, name, pv)
+        return b

@@ -1,0 +1,394 @@
+// api.cu — the C ABI of include/voda_accel.h: contexts, host<->device staging, dispatch.
+//
+// Host-pointer entry points cut the batch into chunks of rounds and run them through a
+// two-slot pipeline (two streams, two staging buffers): the H2D copy of chunk c+1 overlaps
+// the kernel of chunk c and the D2H copy of chunk c-1.  Device-pointer entry points only
+// enqueue kernels on the context's main stream.  Nothing here computes scheduling results on
+// the CPU; without a CUDA device voda_ctx_create fails and no other entry point can be used.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "kernels.h"
+
+using namespace voda;
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+};
+
+struct voda_ctx {
+  int device = 0;
+  int sms = 0;
+  cudaStream_t stream = nullptr;   // *_dev entry points
+  cudaStream_t pipe[2] = {nullptr, nullptr};
+  DevBuf scratch;                  // kernel scratch for the main stream
+  DevBuf pipe_scratch[2];          // kernel scratch per pipeline slot
+  DevBuf stage[2];                 // staged inputs + outputs per pipeline slot
+  int64_t launches = 0;
+  std::string err;
+};
+
+namespace {
+
+thread_local std::string g_err_noctx;
+
+int fail(voda_ctx* c, int code, const std::string& msg) {
+  if (c) c->err = msg; else g_err_noctx = msg;
+  return code;
+}
+int cuda_fail(voda_ctx* c, cudaError_t e, const char* what) {
+  return fail(c, VODA_E_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define CU(call)                                              \
+  do {                                                        \
+    cudaError_t e__ = (call);                                 \
+    if (e__ != cudaSuccess) return cuda_fail(ctx, e__, #call); \
+  } while (0)
+
+int ensure(voda_ctx* ctx, DevBuf& b, size_t bytes, cudaStream_t user) {
+  if (bytes <= b.cap) return VODA_OK;
+  if (b.p) {
+    CU(cudaStreamSynchronize(user));  // the old buffer may still be in use on that stream
+    CU(cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+  }
+  size_t want = bytes + bytes / 8 + 256;
+  cudaError_t e = cudaMalloc(&b.p, want);
+  if (e != cudaSuccess) {
+    b.p = nullptr;
+    return fail(ctx, VODA_E_NOMEM, std::string("cudaMalloc of scratch failed: ") + cudaGetErrorString(e));
+  }
+  b.cap = want;
+  return VODA_OK;
+}
+
+inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
+
+// which arrays a policy reads (DESIGN.md "inputs per policy")
+enum : unsigned {
+  F_SUBMIT = 1, F_FIRST = 2, F_PRIO = 4, F_NUM = 8, F_MIN = 16, F_MAX = 32, F_REM = 64, F_SPEED = 128
+};
+unsigned algo_fields(int algo) {
+  switch (algo) {
+    case VODA_ALGO_FIFO:
+    case VODA_ALGO_ELASTIC_FIFO: return F_SUBMIT | F_MIN | F_MAX;
+    case VODA_ALGO_SRJF:
+    case VODA_ALGO_ELASTIC_SRJF: return F_REM | F_MIN | F_MAX;
+    case VODA_ALGO_TIRESIAS: return F_PRIO | F_FIRST | F_NUM | F_MIN | F_MAX;
+    case VODA_ALGO_ELASTIC_TIRESIAS: return F_PRIO | F_FIRST | F_NUM | F_MIN | F_MAX | F_SPEED;
+    case VODA_ALGO_FFDL_OPTIMIZER: return F_SUBMIT | F_MIN | F_MAX | F_SPEED;
+    case VODA_ALGO_AFSL: return F_SUBMIT | F_MIN | F_MAX | F_REM | F_SPEED;
+  }
+  return 0;
+}
+
+int check_batch(voda_ctx* ctx, const voda_alloc_batch* b) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  if (!b) return fail(ctx, VODA_E_INVALID, "null batch");
+  if (b->algo < 0 || b->algo >= VODA_ALGO_COUNT)
+    return fail(ctx, VODA_E_INVALID, "unknown policy id (NewAlgorithmFactory: Not found)");
+  if (b->rounds < 0) return fail(ctx, VODA_E_INVALID, "negative round count");
+  if (b->rounds > 0 && (!b->job_off || !b->total_gpu)) return fail(ctx, VODA_E_INVALID, "job_off / total_gpu missing");
+  const unsigned f = algo_fields(b->algo);
+  if ((f & F_SUBMIT) && !b->submit_sec) return fail(ctx, VODA_E_INVALID, "policy needs submit_sec");
+  if ((f & F_FIRST) && !b->first_sec) return fail(ctx, VODA_E_INVALID, "policy needs first_sec");
+  if ((f & F_PRIO) && !b->priority) return fail(ctx, VODA_E_INVALID, "policy needs priority");
+  if ((f & F_NUM) && !b->num_proc) return fail(ctx, VODA_E_INVALID, "policy needs num_proc");
+  if ((f & F_MIN) && !b->min_proc) return fail(ctx, VODA_E_INVALID, "policy needs min_proc");
+  if ((f & F_MAX) && !b->max_proc) return fail(ctx, VODA_E_INVALID, "policy needs max_proc");
+  if ((f & F_REM) && !b->remaining_sec) return fail(ctx, VODA_E_INVALID, "policy needs remaining_sec");
+  if ((f & F_SPEED) && (!b->speedup || b->speedup_stride < 1))
+    return fail(ctx, VODA_E_INVALID, "policy needs the speedup table (stride >= 1)");
+  return VODA_OK;
+}
+
+AllocArgs make_args(const voda_alloc_batch* b) {
+  AllocArgs a{};
+  a.algo = b->algo;
+  a.rounds = b->rounds;
+  a.job_base = 0;
+  a.job_off = b->job_off;
+  a.total_gpu = b->total_gpu;
+  a.submit_sec = b->submit_sec;
+  a.submit_nsec = b->submit_nsec;
+  a.first_sec = b->first_sec;
+  a.first_nsec = b->first_nsec;
+  a.priority = b->priority;
+  a.num_proc = b->num_proc;
+  a.min_proc = b->min_proc;
+  a.max_proc = b->max_proc;
+  a.remaining_sec = b->remaining_sec;
+  a.speedup = b->speedup;
+  a.stride = b->speedup_stride;
+  a.queue_num = b->queue_num > 0 ? b->queue_num : 2;                       // tiresias.go:24
+  a.compaction = b->compaction_threshold >= 0 ? b->compaction_threshold : 10;  // elastic_tiresias.go:21
+  a.max_jobs = b->max_jobs;
+  a.max_total = b->max_total_gpu;
+  return a;
+}
+
+// Enqueue the kernels of one policy over `a` on `stream`.
+int dispatch_alloc(voda_ctx* ctx, const AllocArgs& a, DevBuf& scratch, cudaStream_t stream) {
+  if (a.rounds == 0) return VODA_OK;
+  switch (a.algo) {
+    case VODA_ALGO_FFDL_OPTIMIZER: {
+      const int grid = ffdl_grid(ctx->sms, a.rounds);
+      if (ffdl_smem_bytes(a) > 200 * 1024)
+        return fail(ctx, VODA_E_UNSUPPORTED, "FfDL: total_gpu / jobs too large for one CTA's shared memory");
+      const size_t need = ffdl_scratch_bytes(a, grid);
+      int rc = ensure(ctx, scratch, need, stream);
+      if (rc) return rc;
+      CU(launch_ffdl(a, grid, scratch.p, need, stream));
+      ctx->launches += 1;
+      return VODA_OK;
+    }
+    default:
+      return fail(ctx, VODA_E_UNSUPPORTED, "policy kernel not built into this library");
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* voda_version(void) { return "vodascheduler_b200 0.1 (sm_100a)"; }
+
+int voda_ctx_create(int device, voda_ctx** out) {
+  if (!out) return fail(nullptr, VODA_E_INVALID, "null out pointer");
+  *out = nullptr;
+  int count = 0;
+  cudaError_t e = cudaGetDeviceCount(&count);
+  if (e != cudaSuccess || count == 0)
+    return fail(nullptr, VODA_E_CUDA,
+                std::string("no CUDA device: this library has no CPU path (") +
+                    (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0") + ")");
+  if (device < 0 || device >= count) return fail(nullptr, VODA_E_INVALID, "device index out of range");
+  voda_ctx* ctx = new voda_ctx();
+  ctx->device = device;
+  auto bail = [&](cudaError_t err, const char* what) {
+    int rc = cuda_fail(nullptr, err, what);
+    delete ctx;
+    return rc;
+  };
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return bail(e, "cudaSetDevice");
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return bail(e, "cudaGetDeviceProperties");
+  ctx->sms = prop.multiProcessorCount;
+  if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  for (int i = 0; i < 2; i++)
+    if ((e = cudaStreamCreateWithFlags(&ctx->pipe[i], cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  *out = ctx;
+  return VODA_OK;
+}
+
+void voda_ctx_destroy(voda_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaDeviceSynchronize();
+  DevBuf* bufs[] = {&ctx->scratch, &ctx->pipe_scratch[0], &ctx->pipe_scratch[1], &ctx->stage[0], &ctx->stage[1]};
+  for (DevBuf* b : bufs)
+    if (b->p) cudaFree(b->p);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  for (int i = 0; i < 2; i++)
+    if (ctx->pipe[i]) cudaStreamDestroy(ctx->pipe[i]);
+  delete ctx;
+}
+
+void* voda_ctx_stream(voda_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int voda_ctx_sync(voda_ctx* ctx) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  CU(cudaSetDevice(ctx->device));
+  CU(cudaStreamSynchronize(ctx->stream));
+  CU(cudaStreamSynchronize(ctx->pipe[0]));
+  CU(cudaStreamSynchronize(ctx->pipe[1]));
+  return VODA_OK;
+}
+
+int64_t voda_ctx_launch_count(voda_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+const char* voda_last_error(voda_ctx* ctx) { return ctx ? ctx->err.c_str() : g_err_noctx.c_str(); }
+
+const char* voda_status_str(int32_t s) {
+  switch (s) {
+    case VODA_ST_OK: return "ok";
+    case VODA_ST_NEGATIVE: return "Invalid GPU allocations: can't be negative";
+    case VODA_ST_LESS_THAN_MIN: return "Invalid GPU allocations: less than job min gpu";
+    case VODA_ST_EXCEEDED_MAX: return "Invalid GPU allocations: exceeded job max gpu";
+    case VODA_ST_EXCEEDED_TOTAL: return "Invalid GPU allocations: exceeded total GPUs";
+    case VODA_ST_INFEASIBLE: return "infeasible";
+    case VODA_ST_NOT_FOUND: return "Not found";
+    case VODA_ST_NONTERMINATING: return "reference would not terminate";
+    case VODA_ST_BOUND: return "round exceeds the declared max_jobs / max_total_gpu";
+    case VODA_ST_RUNTIME_PANIC: return "runtime error: makeslice: cap out of range";
+  }
+  return "unknown status";
+}
+
+static const char* kAlgoNames[VODA_ALGO_COUNT] = {"FIFO", "ElasticFIFO", "SRJF", "ElasticSRJF",
+                                                  "Tiresias", "ElasticTiresias", "FfDLOptimizer", "AFS-L"};
+
+int voda_algo_from_name(const char* name) {
+  if (!name) return -1;
+  for (int i = 0; i < VODA_ALGO_COUNT; i++)
+    if (std::strcmp(name, kAlgoNames[i]) == 0) return i;
+  return -1;
+}
+const char* voda_algo_name(int32_t algo) {
+  return (algo >= 0 && algo < VODA_ALGO_COUNT) ? kAlgoNames[algo] : "";
+}
+int voda_algo_need_job_info(int32_t algo) {
+  switch (algo) {
+    case VODA_ALGO_SRJF:
+    case VODA_ALGO_ELASTIC_SRJF:
+    case VODA_ALGO_ELASTIC_TIRESIAS:
+    case VODA_ALGO_FFDL_OPTIMIZER:
+    case VODA_ALGO_AFSL: return 1;
+  }
+  return 0;
+}
+
+void* voda_host_alloc(size_t bytes) {
+  void* p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+  return p;
+}
+void voda_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+int voda_allocate_dev(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* d_out_gpus, int32_t* d_out_status) {
+  int rc = check_batch(ctx, b);
+  if (rc) return rc;
+  if (b->rounds == 0) return VODA_OK;
+  if (!d_out_gpus || !d_out_status) return fail(ctx, VODA_E_INVALID, "null output");
+  if (b->max_jobs <= 0 || b->max_total_gpu < 0 || (b->max_total_gpu == 0 && false))
+    return fail(ctx, VODA_E_INVALID, "voda_allocate_dev needs max_jobs (and max_total_gpu) declared");
+  CU(cudaSetDevice(ctx->device));
+  AllocArgs a = make_args(b);
+  a.out_gpus = d_out_gpus;
+  a.out_status = d_out_status;
+  return dispatch_alloc(ctx, a, ctx->scratch, ctx->stream);
+}
+
+int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, int32_t* out_status) {
+  int rc = check_batch(ctx, b);
+  if (rc) return rc;
+  if (b->rounds == 0) return VODA_OK;
+  if (!out_gpus || !out_status) return fail(ctx, VODA_E_INVALID, "null output");
+  CU(cudaSetDevice(ctx->device));
+  const int R = b->rounds;
+  const int32_t* off = b->job_off;
+  if (off[0] != 0) return fail(ctx, VODA_E_INVALID, "job_off[0] must be 0");
+  int max_jobs = b->max_jobs, max_total = b->max_total_gpu;
+  if (max_jobs <= 0 || max_total <= 0) {
+    int mj = 0, mt = 0;
+    for (int r = 0; r < R; r++) {
+      int n = off[r + 1] - off[r];
+      if (n < 0) return fail(ctx, VODA_E_INVALID, "job_off must ascend");
+      mj = std::max(mj, n);
+      mt = std::max(mt, b->total_gpu[r]);
+    }
+    if (max_jobs <= 0) max_jobs = std::max(mj, 1);
+    if (max_total <= 0) max_total = mt;
+  }
+  const unsigned f = algo_fields(b->algo);
+  const size_t W = (f & F_SPEED) ? (size_t)b->speedup_stride : 0;
+  // bytes staged per job / per round
+  size_t per_job = 4 /*out*/;
+  if (f & F_SUBMIT) per_job += 8 + (b->submit_nsec ? 4 : 0);
+  if (f & F_FIRST) per_job += 8 + (b->first_nsec ? 4 : 0);
+  if (f & F_PRIO) per_job += 4;
+  if (f & F_NUM) per_job += 4;
+  if (f & F_MIN) per_job += 4;
+  if (f & F_MAX) per_job += 4;
+  if (f & F_REM) per_job += 4;
+  per_job += 4 * W;
+  // chunking: ~8 MiB of staged bytes per chunk, at least 4 chunks when the batch allows
+  const size_t total_bytes = per_job * (size_t)off[R] + 12 * (size_t)R;
+  size_t target = 8u << 20;
+  int chunks = (int)std::min<size_t>((size_t)R, std::max<size_t>(1, (total_bytes + target - 1) / target));
+  if (chunks < 4 && R >= 4 && total_bytes > (1u << 20)) chunks = 4;
+  const int rounds_per = (R + chunks - 1) / chunks;
+
+  for (int c = 0, r0 = 0; r0 < R; c++, r0 += rounds_per) {
+    const int r1 = std::min(R, r0 + rounds_per);
+    const int slot = c & 1;
+    cudaStream_t s = ctx->pipe[slot];
+    const int j0 = off[r0], j1 = off[r1];
+    const size_t nj = (size_t)(j1 - j0), nr = (size_t)(r1 - r0);
+    // carve the staging buffer
+    size_t pos = 0;
+    auto carve = [&](size_t bytes) { size_t at = pos; pos += align256(bytes ? bytes : 1); return at; };
+    struct Copy { size_t at; const void* src; size_t bytes; };
+    std::vector<Copy> copies;
+    auto in = [&](const void* base, size_t elem, size_t first, size_t count) -> size_t {
+      size_t at = carve(elem * count);
+      if (count) copies.push_back({at, (const char*)base + elem * first, elem * count});
+      return at;
+    };
+    const size_t o_off = in(off, 4, (size_t)r0, nr + 1);
+    const size_t o_tot = in(b->total_gpu, 4, (size_t)r0, nr);
+    size_t o_ss = 0, o_sn = 0, o_fs = 0, o_fn = 0, o_pr = 0, o_np = 0, o_mn = 0, o_mx = 0, o_rm = 0, o_sp = 0;
+    if (f & F_SUBMIT) { o_ss = in(b->submit_sec, 8, j0, nj); if (b->submit_nsec) o_sn = in(b->submit_nsec, 4, j0, nj); }
+    if (f & F_FIRST) { o_fs = in(b->first_sec, 8, j0, nj); if (b->first_nsec) o_fn = in(b->first_nsec, 4, j0, nj); }
+    if (f & F_PRIO) o_pr = in(b->priority, 4, j0, nj);
+    if (f & F_NUM) o_np = in(b->num_proc, 4, j0, nj);
+    if (f & F_MIN) o_mn = in(b->min_proc, 4, j0, nj);
+    if (f & F_MAX) o_mx = in(b->max_proc, 4, j0, nj);
+    if (f & F_REM) o_rm = in(b->remaining_sec, 4, j0, nj);
+    if (f & F_SPEED) o_sp = in(b->speedup, 4 * W, j0, nj);
+    const size_t o_og = carve(4 * nj), o_os = carve(4 * nr);
+    rc = ensure(ctx, ctx->stage[slot], pos, s);
+    if (rc) return rc;
+    char* base = (char*)ctx->stage[slot].p;
+    for (const Copy& cp : copies) CU(cudaMemcpyAsync(base + cp.at, cp.src, cp.bytes, cudaMemcpyHostToDevice, s));
+    AllocArgs a = make_args(b);
+    a.rounds = (int)nr;
+    a.job_base = j0;
+    a.max_jobs = max_jobs;
+    a.max_total = max_total;
+    a.job_off = (const int32_t*)(base + o_off);
+    a.total_gpu = (const int32_t*)(base + o_tot);
+    a.submit_sec = (f & F_SUBMIT) ? (const int64_t*)(base + o_ss) : nullptr;
+    a.submit_nsec = ((f & F_SUBMIT) && b->submit_nsec) ? (const int32_t*)(base + o_sn) : nullptr;
+    a.first_sec = (f & F_FIRST) ? (const int64_t*)(base + o_fs) : nullptr;
+    a.first_nsec = ((f & F_FIRST) && b->first_nsec) ? (const int32_t*)(base + o_fn) : nullptr;
+    a.priority = (f & F_PRIO) ? (const int32_t*)(base + o_pr) : nullptr;
+    a.num_proc = (f & F_NUM) ? (const int32_t*)(base + o_np) : nullptr;
+    a.min_proc = (f & F_MIN) ? (const int32_t*)(base + o_mn) : nullptr;
+    a.max_proc = (f & F_MAX) ? (const int32_t*)(base + o_mx) : nullptr;
+    a.remaining_sec = (f & F_REM) ? (const float*)(base + o_rm) : nullptr;
+    a.speedup = (f & F_SPEED) ? (const float*)(base + o_sp) : nullptr;
+    a.out_gpus = (int32_t*)(base + o_og);
+    a.out_status = (int32_t*)(base + o_os);
+    rc = dispatch_alloc(ctx, a, ctx->pipe_scratch[slot], s);
+    if (rc) return rc;
+    if (nj) CU(cudaMemcpyAsync(out_gpus + j0, base + o_og, 4 * nj, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(out_status + r0, base + o_os, 4 * nr, cudaMemcpyDeviceToHost, s));
+  }
+  CU(cudaStreamSynchronize(ctx->pipe[0]));
+  CU(cudaStreamSynchronize(ctx->pipe[1]));
+  return VODA_OK;
+}
+
+int voda_munkres_max(voda_ctx* ctx, int32_t, int32_t, const int64_t*, int32_t*, int32_t*) {
+  return fail(ctx, VODA_E_UNSUPPORTED, "munkres kernel not built into this library");
+}
+int voda_munkres_max_dev(voda_ctx* ctx, int32_t, int32_t, const int64_t*, int32_t*, int32_t*) {
+  return fail(ctx, VODA_E_UNSUPPORTED, "munkres kernel not built into this library");
+}
+int voda_place(voda_ctx* ctx, const voda_place_batch*, const voda_place_out*) {
+  return fail(ctx, VODA_E_UNSUPPORTED, "placement kernel not built into this library");
+}
+int voda_place_dev(voda_ctx* ctx, const voda_place_batch*, const voda_place_out*) {
+  return fail(ctx, VODA_E_UNSUPPORTED, "placement kernel not built into this library");
+}
+
+}  // extern "C"

@@ -1,0 +1,133 @@
+// common.cuh — shared device helpers for the allocation kernels (sm_100a).
+//
+// Every kernel here follows the same shape: one CTA owns one scheduling round at a time
+// (rounds are independent; a persistent grid strides over them), the round's per-job state
+// lives in shared memory, and the float32 arithmetic is written operation by operation in the
+// reference's evaluation order.  The library is compiled with -fmad=false and without
+// fast-math so nvcc neither contracts a*b+c nor relaxes IEEE division.
+#pragma once
+
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/voda_accel.h"
+
+namespace voda {
+
+// Kernel-side view of a voda_alloc_batch: device pointers only, plus the outputs.
+struct AllocArgs {
+  int32_t algo, rounds;
+  int32_t job_base;  // job_off values are absolute; the job arrays start at this job
+  const int32_t* job_off;
+  const int32_t* total_gpu;
+  const int64_t* submit_sec;
+  const int32_t* submit_nsec;
+  const int64_t* first_sec;
+  const int32_t* first_nsec;
+  const int32_t* priority;
+  const int32_t* num_proc;
+  const int32_t* min_proc;
+  const int32_t* max_proc;
+  const float* remaining_sec;
+  const float* speedup;
+  int32_t stride;      // speedup table width W
+  int32_t queue_num;   // TiresiasQueueNum
+  int32_t compaction;  // ElasticTiresiasCompactionThreshold
+  int32_t max_jobs;    // declared upper bound of jobs per round
+  int32_t max_total;   // declared upper bound of total_gpu
+  int32_t* out_gpus;
+  int32_t* out_status;
+};
+
+__host__ __device__ inline int next_pow2(int x) {
+  int p = 1;
+  while (p < x) p <<= 1;
+  return p;
+}
+
+#define VODA_NEG_INF (__int_as_float(0xff800000))
+
+// Order-preserving image of a float32 sort key under Go's `<` (-0 == +0; NaN out of domain).
+__device__ __forceinline__ int64_t f32_order_key(float x) {
+  int32_t b = __float_as_int(x);
+  int32_t mag = b & 0x7fffffff;  // -0 and +0 both map to 0
+  return b >= 0 ? (int64_t)mag : -(int64_t)mag;
+}
+
+// Strict total order on job slots: (hi, lo, slot) with slots >= n acting as +infinity.
+// Because the slot index is the last component, sorting with it yields exactly the result
+// of a STABLE sort by (hi, lo) — what sort.SliceStable produces in the reference.
+__device__ __forceinline__ bool key_less(const int64_t* hi, const int32_t* lo, int n, int a, int b) {
+  if (b >= n) return a < n ? true : a < b;
+  if (a >= n) return false;
+  int64_t ha = hi[a], hb = hi[b];
+  if (ha != hb) return ha < hb;
+  int32_t la = lo[a], lb = lo[b];
+  if (la != lb) return la < lb;
+  return a < b;
+}
+
+// Block-wide bitonic argsort: perm[0..P) <- slots ordered by key_less; P = pow2 >= n.
+// All threads of the CTA must call it.
+__device__ inline void block_argsort(const int64_t* hi, const int32_t* lo, int* perm, int n, int P) {
+  for (int i = threadIdx.x; i < P; i += blockDim.x) perm[i] = i;
+  __syncthreads();
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int i = threadIdx.x; i < P; i += blockDim.x) {
+        int ixj = i ^ j;
+        if (ixj > i) {
+          int a = perm[i], b = perm[ixj];
+          bool up = (i & k) == 0;
+          bool a_after_b = key_less(hi, lo, n, b, a);
+          if (a_after_b == up) {
+            perm[i] = b;
+            perm[ixj] = a;
+          }
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// validateResult (pkg/algorithm/utils.go:18-42) over one round; all threads call.
+// `skip` (may be null) marks jobs absent from the reference's result map.
+// s_red: two 64-bit words of shared memory.  Returns the round status (tie rule: smallest
+// code among the offending jobs, then the total check).
+__device__ inline int block_validate(const AllocArgs& a, int o, int n, int total, const int32_t* r,
+                                     const unsigned char* skip, long long* s_red) {
+  if (threadIdx.x == 0) {
+    s_red[0] = 99;
+    s_red[1] = 0;
+  }
+  __syncthreads();
+  int worst = 99;
+  long long sum = 0;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    if (skip && skip[i]) continue;
+    int v = r[i];
+    int st = 99;
+    if (v < 0) st = VODA_ST_NEGATIVE;
+    else if (v > 0 && v < a.min_proc[o + i]) st = VODA_ST_LESS_THAN_MIN;
+    else if (v > a.max_proc[o + i]) st = VODA_ST_EXCEEDED_MAX;
+    worst = min(worst, st);
+    sum += v;
+  }
+  for (int d = 16; d > 0; d >>= 1) {
+    worst = min(worst, __shfl_xor_sync(0xffffffffu, worst, d));
+    sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  }
+  if ((threadIdx.x & 31) == 0) {
+    atomicMin(reinterpret_cast<int*>(&s_red[0]), worst);
+    atomicAdd(reinterpret_cast<unsigned long long*>(&s_red[1]), (unsigned long long)sum);
+  }
+  __syncthreads();
+  int st = *reinterpret_cast<int*>(&s_red[0]);
+  long long tot = s_red[1];
+  __syncthreads();
+  if (st != 99) return st;
+  return tot > (long long)total ? VODA_ST_EXCEEDED_TOTAL : VODA_ST_OK;
+}
+
+}  // namespace voda

@@ -1,0 +1,3 @@
+"""Which reference policies have a CUDA kernel in this build (names of
+NewAlgorithmFactory, pkg/algorithm/types.go:26-47)."""
+SUPPORTED_ALGOS = ("FfDLOptimizer",)
