@@ -143,6 +143,30 @@ int voda_allocate_dev(voda_ctx* ctx, const voda_alloc_batch* dev_batch,
                       int32_t* d_out_gpus, int32_t* d_out_status);
 
 /*
+ * FfDL Optimizer rounds for callers that cannot allocate device memory.  This entry point has
+ * no counterpart in the reference.  It computes exactly what voda_allocate_dev computes for
+ * algo == VODA_ALGO_FFDL_OPTIMIZER (every pointer, inside the struct too, is a device pointer;
+ * max_jobs and max_total_gpu must be declared; `algo` is ignored), but it never calls
+ * cudaMalloc / cudaFree: the kernel's SOL scratch is a fixed 32 MiB array inside the library
+ * image (held by every GPU that loads the library until the process exits) instead of a
+ * buffer the context grows on demand.  Use it when the GPU's memory already belongs to
+ * someone else's allocator, or when the calling thread cannot afford the device-wide stall
+ * of an allocation.  No voda_ctx is needed: it runs on the CURRENT device, on `stream`
+ * (a cudaStream_t, NULL = default stream), asynchronously.
+ *   - Shapes whose per-round scratch, min(max_jobs, max_total_gpu) * ceil(max_total_gpu/4) * 8
+ *     bytes, exceeds 32 MiB are refused with VODA_E_TOO_LARGE and a message in errbuf.
+ *   - All calls on a GPU share the array (it keeps the previous call's bytes; nothing needs
+ *     clearing because every SOL row is rewritten before it is read).  Calls that overlap on
+ *     the GPU race on it: serialise them.
+ *   - The first call on each device looks up the array's device address; make that call
+ *     before any stream capture on the device.
+ * errbuf (may be NULL) receives a NUL-terminated message when the result is not VODA_OK.
+ */
+int voda_ffdl_allocate_static(void* stream, const voda_alloc_batch* dev_batch,
+                              int32_t* d_out_gpus, int32_t* d_out_status,
+                              char* errbuf, size_t errbuf_len);
+
+/*
  * Replaces m := munkres.NewMatrix(n); m.A = A; munkres.ComputeMunkresMax(m)
  * (github.com/heyfey/munkres@d4f16a25250d, not vendored; call site
  * pkg/placement/placement_manager.go:505-512) for `batch` independent n x n matrices.

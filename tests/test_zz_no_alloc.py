@@ -1,0 +1,77 @@
+"""voda_ffdl_allocate_static — the entry point for hosts that must not allocate GPU memory
+(their HBM is owned by another allocator, or they cannot take the device-wide stall of a
+cudaMalloc).  It keeps the FfDL kernel's SOL scratch in a fixed array inside the library
+instead of a buffer grown on demand, so it must give exactly the answers of the ordinary
+entry point, call after call, while sharing that one array between calls.
+
+Collected last on purpose (file name): a failure here cannot hide other tests in a -x run.
+Works alone in a fresh process and after the rest of the suite (it creates its own context
+and shares no state with other tests).
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from vodascheduler_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _run_both(ctx, lib, batch):
+    import torch
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)  # the static entry point runs on the current device
+    db = batch.to_device(dev)
+    ref_g = torch.zeros(batch.jobs, dtype=torch.int32, device=dev)
+    ref_s = torch.full((batch.rounds,), -1, dtype=torch.int32, device=dev)
+    ctx.allocate_dev(db, ref_g, ref_s)
+    ctx.sync()
+    got_g = torch.full((batch.jobs,), -7, dtype=torch.int32, device=dev)
+    got_s = torch.full((batch.rounds,), -7, dtype=torch.int32, device=dev)
+    err = C.create_string_buffer(256)
+    s = db.struct()
+    rc = lib.voda_ffdl_allocate_static(None, C.byref(s), got_g.data_ptr(), got_s.data_ptr(), err, len(err))
+    assert rc == 0, err.value.decode()
+    torch.cuda.synchronize()
+    return ref_g.cpu().numpy(), ref_s.cpu().numpy(), got_g.cpu().numpy(), got_s.cpu().numpy()
+
+
+def test_static_scratch_matches_allocating_entry_point_twice():
+    """Two calls in a row (different batches, so the second one finds the first one's bytes in
+    the shared array) both equal voda_allocate_dev bit for bit — allocations and statuses."""
+    from vodascheduler_b200 import Context
+    ctx = Context(0)
+    try:
+        lib = ctx._lib
+        first = synth.jobs_batch("FfDLOptimizer", rounds=300, jobs_per_round=96, total_gpu=320, ragged=True)
+        second = synth.quirk_batch("FfDLOptimizer", rounds=500, jobs_per_round=48, total_gpu=200, seed=99)
+        for batch in (first, second):
+            ref_g, ref_s, got_g, got_s = _run_both(ctx, lib, batch)
+            assert np.array_equal(got_s, ref_s)
+            assert np.array_equal(got_g, ref_g)
+        assert (ref_s != 0).any()  # the second batch exercises the panic statuses too
+    finally:
+        ctx.close()
+
+
+def test_static_scratch_rejects_oversize_shape():
+    """A shape whose single-round scratch exceeds the fixed 32 MiB is refused with a message,
+    before anything is launched."""
+    import torch
+    from vodascheduler_b200 import Context, _abi
+    ctx = Context(0)
+    try:
+        torch.cuda.set_device(0)
+        b = synth.jobs_batch("FfDLOptimizer", rounds=2, jobs_per_round=8, total_gpu=16)
+        db = b.to_device(torch.device("cuda", 0))
+        db.max_jobs, db.max_total_gpu = 4096, 8192  # 4096 * 2048 * 8 B = 64 MiB per round
+        out = torch.zeros(b.jobs, dtype=torch.int32, device="cuda")
+        st = torch.zeros(b.rounds, dtype=torch.int32, device="cuda")
+        err = C.create_string_buffer(256)
+        s = db.struct()
+        rc = ctx._lib.voda_ffdl_allocate_static(None, C.byref(s), out.data_ptr(), st.data_ptr(), err, len(err))
+        assert rc == _abi.E_TOO_LARGE
+        assert b"exceeds the static scratch" in err.value
+    finally:
+        ctx.close()

@@ -71,6 +71,8 @@ PROTOTYPES = {
     "voda_host_free": (None, [C.c_void_p]),
     "voda_allocate": (C.c_int, [C.c_void_p, C.POINTER(AllocBatchStruct), C.c_void_p, C.c_void_p]),
     "voda_allocate_dev": (C.c_int, [C.c_void_p, C.POINTER(AllocBatchStruct), C.c_void_p, C.c_void_p]),
+    "voda_ffdl_allocate_static": (C.c_int, [C.c_void_p, C.POINTER(AllocBatchStruct), C.c_void_p, C.c_void_p,
+                                            C.c_char_p, C.c_size_t]),
     "voda_munkres_max": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "voda_munkres_max_dev": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "voda_place": (C.c_int, [C.c_void_p, C.POINTER(PlaceBatchStruct), C.POINTER(PlaceOutStruct)]),
