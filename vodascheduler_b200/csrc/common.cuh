@@ -67,9 +67,10 @@ __device__ __forceinline__ bool key_less(const int64_t* hi, const int32_t* lo, i
   return a < b;
 }
 
-// Block-wide bitonic argsort: perm[0..P) <- slots ordered by key_less; P = pow2 >= n.
-// All threads of the CTA must call it.
-__device__ inline void block_argsort(const int64_t* hi, const int32_t* lo, int* perm, int n, int P) {
+// Block-wide bitonic argsort: perm[0..P) <- slots ordered by the strict total order `less`
+// (slots >= n must sort last); P = pow2 >= n.  All threads of the CTA must call it.
+template <typename Less>
+__device__ inline void block_argsort_by(int* perm, int P, Less less) {
   for (int i = threadIdx.x; i < P; i += blockDim.x) perm[i] = i;
   __syncthreads();
   for (int k = 2; k <= P; k <<= 1) {
@@ -79,7 +80,7 @@ __device__ inline void block_argsort(const int64_t* hi, const int32_t* lo, int* 
         if (ixj > i) {
           int a = perm[i], b = perm[ixj];
           bool up = (i & k) == 0;
-          bool a_after_b = key_less(hi, lo, n, b, a);
+          bool a_after_b = less(b, a);
           if (a_after_b == up) {
             perm[i] = b;
             perm[ixj] = a;
@@ -89,6 +90,65 @@ __device__ inline void block_argsort(const int64_t* hi, const int32_t* lo, int* 
       __syncthreads();
     }
   }
+}
+
+__device__ inline void block_argsort(const int64_t* hi, const int32_t* lo, int* perm, int n, int P) {
+  block_argsort_by(perm, P, [=](int a, int b) { return key_less(hi, lo, n, a, b); });
+}
+
+// "Give need[i] while it fits", in order i = 0..n-1:  if free >= need[i] { take; free -= need[i] }.
+// The dependence on `free` is serial (a job that does not fit is skipped and a later, smaller
+// one may fit), so ONE WARP evaluates it, 32 jobs at a time: prefix sums find the first job
+// that fails given that all pending ones before it were accepted; it is rejected and the rest
+// of the chunk is re-evaluated.  Exact for any sign of need[].  Call with a full warp; writes
+// acc[i] in {0,1} and returns the remaining free (same value in every lane).
+__device__ inline long long warp_skip_scan(const int32_t* need, int n, long long free, unsigned char* acc) {
+  const unsigned full = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  for (int base = 0; base < n; base += 32) {
+    const int i = base + lane;
+    const bool valid = i < n;
+    const long long m = valid ? need[i] : 0;
+    bool pending = valid;
+    bool accepted = false;
+    const bool anyNeg = __any_sync(full, valid && m < 0);
+    while (true) {
+      unsigned pend = __ballot_sync(full, pending);
+      if (!pend) break;
+      if (!anyNeg) {
+        // free never grows inside the chunk: jobs larger than it can be rejected at once
+        const bool hopeless = pending && m > free;
+        const unsigned h = __ballot_sync(full, hopeless);
+        if (h) {
+          if (hopeless) pending = false;
+          pend &= ~h;
+          if (!pend) break;
+        }
+      }
+      long long incl = pending ? m : 0;  // inclusive prefix of need over pending lanes
+      for (int d = 1; d < 32; d <<= 1) {
+        long long up = __shfl_up_sync(full, incl, d);
+        if (lane >= d) incl += up;
+      }
+      const long long excl = incl - (pending ? m : 0);
+      const bool fits = pending && (free - excl >= m);
+      const unsigned failMask = __ballot_sync(full, pending && !fits);
+      if (!failMask) {  // everything pending is accepted
+        if (pending) accepted = true;
+        free -= __shfl_sync(full, incl, 31 - __clz(pend));
+        break;
+      }
+      const int f = __ffs(failMask) - 1;  // first failing lane: rejected; pending lanes before it accepted
+      if (pending && lane < f) {
+        accepted = true;
+        pending = false;
+      }
+      if (lane == f) pending = false;
+      free -= __shfl_sync(full, excl, f);
+    }
+    if (valid) acc[i] = accepted ? 1 : 0;
+  }
+  return free;
 }
 
 // validateResult (pkg/algorithm/utils.go:18-42) over one round; all threads call.

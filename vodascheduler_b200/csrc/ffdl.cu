@@ -26,7 +26,7 @@ namespace voda {
 
 namespace {
 
-constexpr int kThreads = 256;
+constexpr int kThreads = 64;
 
 struct FfdlSmem {
   float4* rowA;      // [G4]  row buffers, group q = P[4q-3 .. 4q]
@@ -47,45 +47,85 @@ __device__ __forceinline__ float4 ld_group(const float4* row, int q) {
   return row[q];
 }
 
-#define VODA_CELL(c, s, gval)                      \
-  {                                                \
-    float p = sv[s] + v[3 + (c) - (s)];            \
-    bool take = p > best[c];                       \
-    best[c] = take ? p : best[c];                  \
-    bg[c] = take ? (gval) : bg[c];                 \
+// One (cell, g) step of  p = S + P[j-1][k-g]; if p > best { best = p; SOL = g }.
+// Instruction mix matters here (the loop is bound by the ALU pipe): the running maximum is an
+// FMNMX, the "did it win" bit an FSET (1.0f / 0.0f), and the winning g is NOT tracked with a
+// select per step: the win bits are shifted into a float accumulator with an FFMA
+// (acc = acc*2 + bit, exact below 2^24), i.e. on the FMA pipe, and the last win is decoded
+// once per flush.  fmaxf(best, p) equals the reference's strict-'>' select for every non-NaN
+// input (equal values are interchangeable; a NaN p never replaces best in either form).
+#define VODA_CELL(c, s)                              \
+  {                                                  \
+    const float p = sv[s] + v[3 + (c) - (s)];        \
+    const float t = (p > best[c]) ? 1.0f : 0.0f;     \
+    best[c] = fmaxf(best[c], p);                     \
+    acc[c] = fmaf(acc[c], 2.0f, t);                  \
   }
 
-// One DP row for column tile `tq` (cells k = 4*tq+1 .. 4*tq+4).
+constexpr int kCells = 16;              // adjacent cells per thread
+constexpr int kGroups = kCells / 4 + 1;  // float4 groups of row j-1 in the sliding window
+constexpr int kFlushBlocks = 6;          // 6 blocks x 4 g-steps = 24 win bits per accumulator flush
+
+// One DP row for column tile `tq` (cells k = kCells*tq+1 .. kCells*tq+kCells).
+// Row storage: group q = P[4q-3 .. 4q].  For the block of g = 4m+1 .. 4m+4 the cells need
+// P[base-3 .. base+kCells-1], base = kCells*tq - 4m, i.e. groups q0 .. q0+kCells/4 with
+// q0 = (kCells/4)*tq - m; the next block slides the window down by one group (one LDS.128).
 template <typename SolT>
 __device__ __forceinline__ void ffdl_row_tile(const float4* __restrict__ prev, float4* __restrict__ cur,
                                               const float* __restrict__ srow, int tq, int nblk,
                                               int gslow0, int gslow1, SolT* __restrict__ solrow) {
-  float best[4] = {-10000.0f, -10000.0f, -10000.0f, -10000.0f};
-  int bg[4] = {0, 0, 0, 0};
-  float4 hi = ld_group(prev, tq + 1);
-  float4 lo = ld_group(prev, tq);
+  float best[kCells];
+  float acc[kCells];
+  int bg[kCells];
+#pragma unroll
+  for (int c = 0; c < kCells; c++) {
+    best[c] = -10000.0f;
+    acc[c] = 0.0f;
+    bg[c] = 0;
+  }
+  const int qtop = (kCells / 4) * tq;
+  float4 grp[kGroups];
+#pragma unroll
+  for (int i = 0; i < kGroups; i++) grp[i] = ld_group(prev, qtop + i);
   const float4* s4 = reinterpret_cast<const float4*>(srow);
+  int sinceFlush = 0;
   for (int m = 0; m < nblk; m++) {
-    float v[8] = {lo.x, lo.y, lo.z, lo.w, hi.x, hi.y, hi.z, hi.w};
-    float4 sq = s4[m];
-    float sv[4] = {sq.x, sq.y, sq.z, sq.w};
-    const int g0 = 4 * m + 1;
+    float v[4 * kGroups];
+#pragma unroll
+    for (int i = 0; i < kGroups; i++) {
+      v[4 * i + 0] = grp[i].x;
+      v[4 * i + 1] = grp[i].y;
+      v[4 * i + 2] = grp[i].z;
+      v[4 * i + 3] = grp[i].w;
+    }
+    const float4 sq = s4[m];
+    const float sv[4] = {sq.x, sq.y, sq.z, sq.w};
 #pragma unroll
     for (int s = 0; s < 4; s++) {
-      VODA_CELL(0, s, g0 + s)
-      VODA_CELL(1, s, g0 + s)
-      VODA_CELL(2, s, g0 + s)
-      VODA_CELL(3, s, g0 + s)
+#pragma unroll
+      for (int c = 0; c < kCells; c++) VODA_CELL(c, s)
     }
-    hi = lo;
-    lo = ld_group(prev, tq - m - 1);
+#pragma unroll
+    for (int i = kGroups - 1; i > 0; i--) grp[i] = grp[i - 1];
+    grp[0] = ld_group(prev, qtop - m - 1);
+    if (++sinceFlush == kFlushBlocks || m == nblk - 1) {
+      // decode the last win of the flushed span: bit b (from the LSB) is g = gEnd - b
+      const int gEnd = 4 * m + 4;
+#pragma unroll
+      for (int c = 0; c < kCells; c++) {
+        const int bits = __float2int_rz(acc[c]);
+        if (bits) bg[c] = gEnd - (__ffs(bits) - 1);
+        acc[c] = 0.0f;
+      }
+      sinceFlush = 0;
+    }
   }
   // g beyond the dense speedup table: the Go map misses, S = 0 (rare: max_j >= W)
   if (gslow1 >= gslow0) {
     const float* pf = reinterpret_cast<const float*>(prev);
 #pragma unroll
-    for (int c = 0; c < 4; c++) {
-      const int k = 4 * tq + 1 + c;
+    for (int c = 0; c < kCells; c++) {
+      const int k = kCells * tq + 1 + c;
       for (int g = gslow0; g <= gslow1 && g <= k; g++) {
         float p = 0.0f + pf[k - g + 3];
         if (p > best[c]) {
@@ -95,28 +135,35 @@ __device__ __forceinline__ void ffdl_row_tile(const float4* __restrict__ prev, f
       }
     }
   }
-  cur[tq + 1] = make_float4(best[0], best[1], best[2], best[3]);
+#pragma unroll
+  for (int i = 0; i < kCells / 4; i++)
+    cur[qtop + 1 + i] = make_float4(best[4 * i], best[4 * i + 1], best[4 * i + 2], best[4 * i + 3]);
   if (sizeof(SolT) == 1) {
-    uint32_t w = (uint32_t)bg[0] | ((uint32_t)bg[1] << 8) | ((uint32_t)bg[2] << 16) | ((uint32_t)bg[3] << 24);
-    reinterpret_cast<uint32_t*>(solrow)[tq] = w;
+    uint32_t w[kCells / 4];
+#pragma unroll
+    for (int i = 0; i < kCells / 4; i++)
+      w[i] = (uint32_t)bg[4 * i] | ((uint32_t)bg[4 * i + 1] << 8) | ((uint32_t)bg[4 * i + 2] << 16) |
+             ((uint32_t)bg[4 * i + 3] << 24);
+    reinterpret_cast<uint4*>(solrow)[tq] = make_uint4(w[0], w[1], w[2], w[3]);
   } else {
-    uint2 w;
-    w.x = (uint32_t)bg[0] | ((uint32_t)bg[1] << 16);
-    w.y = (uint32_t)bg[2] | ((uint32_t)bg[3] << 16);
-    reinterpret_cast<uint2*>(solrow)[tq] = w;
+    uint32_t w[kCells / 2];
+#pragma unroll
+    for (int i = 0; i < kCells / 2; i++) w[i] = (uint32_t)bg[2 * i] | ((uint32_t)bg[2 * i + 1] << 16);
+    reinterpret_cast<uint4*>(solrow)[2 * tq] = make_uint4(w[0], w[1], w[2], w[3]);
+    reinterpret_cast<uint4*>(solrow)[2 * tq + 1] = make_uint4(w[4], w[5], w[6], w[7]);
   }
 }
 
 // All DP rows of one round.  Returns with the last row in `*last` (shared memory).
 template <typename SolT>
-__device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, int K, int K4,
+__device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, int K, int KT,
                           int SW, size_t solStride, unsigned char* solSlab, const float4** last) {
   const int tid = threadIdx.x;
   const int W = a.stride;
   float4* prev = sm.rowA;
   float4* cur = sm.rowB;
   // row 0: P[0][k] = 0 for every k (:80-82)
-  for (int q = tid; q <= K4; q += kThreads)
+  for (int q = tid; q <= (kCells / 4) * KT; q += kThreads)
     prev[q] = q == 0 ? make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, 0.0f) : make_float4(0.f, 0.f, 0.f, 0.f);
   // stage S of row 1
   auto s_value = [&](int j, int g) -> float {  // value of srow slot g-1 for sorted job j (1-based)
@@ -145,7 +192,7 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, 
     const int gt = min(gmax, W - 1);
     const int nblk = gt > 0 ? (gt + 3) >> 2 : 0;
     SolT* solrow = reinterpret_cast<SolT*>(solSlab + (size_t)(j - 1) * solStride);
-    for (int tq = tid; tq < K4; tq += kThreads)
+    for (int tq = tid; tq < KT; tq += kThreads)
       ffdl_row_tile<SolT>(prev, cur, srow, tq, nblk, max(W, 1), gmax, solrow);
     if (tid == 0) cur[0] = make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, -10000.0f);  // P[j][0]
     if (j < J) {
@@ -225,11 +272,11 @@ __global__ void __launch_bounds__(kThreads) ffdl_kernel(AllocArgs a, unsigned ch
       __syncthreads();
       const int gmaxRound = min(sm.misc[0], K);
       // 3-4. DP rows
-      const int K4 = (K + 3) >> 2;
+      const int KT = (K + kCells - 1) / kCells;
       const float4* last = nullptr;
       if (gmaxRound <= 255) {
         const size_t solStride = (size_t)K4cap * 4;
-        ffdl_rows<uint8_t>(a, sm, o, J, K, K4, SW, solStride, slab, &last);
+        ffdl_rows<uint8_t>(a, sm, o, J, K, KT, SW, solStride, slab, &last);
         const float PJK = reinterpret_cast<const float*>(last)[K + 3];
         if (PJK <= 0.0f) {
           st = VODA_ST_INFEASIBLE;
@@ -243,7 +290,7 @@ __global__ void __launch_bounds__(kThreads) ffdl_kernel(AllocArgs a, unsigned ch
         }
       } else {
         const size_t solStride = (size_t)K4cap * 8;
-        ffdl_rows<uint16_t>(a, sm, o, J, K, K4, SW, solStride, slab, &last);
+        ffdl_rows<uint16_t>(a, sm, o, J, K, KT, SW, solStride, slab, &last);
         const float PJK = reinterpret_cast<const float*>(last)[K + 3];
         if (PJK <= 0.0f) {
           st = VODA_ST_INFEASIBLE;
@@ -267,13 +314,13 @@ __global__ void __launch_bounds__(kThreads) ffdl_kernel(AllocArgs a, unsigned ch
 }  // namespace
 
 int ffdl_grid(int sms, int rounds) {
-  int g = sms * 8;
+  int g = sms * 8;  // resident CTAs per SM (64 threads each)
   return rounds < g ? (rounds > 0 ? rounds : 1) : g;
 }
 
 static void ffdl_shape(const AllocArgs& a, int* K4cap, int* SW, int* Jp, size_t* smem) {
   const int Kmax = a.max_total > 0 ? a.max_total : 1;
-  *K4cap = (Kmax + 3) / 4;
+  *K4cap = (kCells / 4) * ((Kmax + kCells - 1) / kCells);  // row groups of 4 cells, whole tiles
   int sw = a.stride - 1 < Kmax ? a.stride - 1 : Kmax;
   if (sw < 1) sw = 1;
   *SW = (sw + 3) & ~3;

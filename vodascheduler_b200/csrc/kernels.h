@@ -14,4 +14,16 @@ size_t ffdl_smem_bytes(const AllocArgs& a);
 cudaError_t launch_ffdl(const AllocArgs& a, int grid, void* scratch, size_t scratch_bytes,
                         cudaStream_t stream);
 
+// FIFO / SRJF / ElasticFIFO / ElasticSRJF (fill.cu)
+size_t fill_smem_bytes(const AllocArgs& a);
+cudaError_t launch_fill(const AllocArgs& a, int sms, cudaStream_t stream);
+
+// Tiresias / ElasticTiresias (tiresias.cu)
+size_t tiresias_smem_bytes(const AllocArgs& a, bool* table_in_smem);
+cudaError_t launch_tiresias(const AllocArgs& a, int sms, cudaStream_t stream);
+
+// AFS-L (afsl.cu)
+size_t afsl_smem_bytes(const AllocArgs& a);
+cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream);
+
 }  // namespace voda
