@@ -148,6 +148,31 @@ int dispatch_alloc(voda_ctx* ctx, const AllocArgs& a, DevBuf& scratch, cudaStrea
       ctx->launches += 1;
       return VODA_OK;
     }
+    case VODA_ALGO_FIFO:
+    case VODA_ALGO_SRJF:
+    case VODA_ALGO_ELASTIC_FIFO:
+    case VODA_ALGO_ELASTIC_SRJF: {
+      if (fill_smem_bytes(a) > 200 * 1024)
+        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
+      CU(launch_fill(a, ctx->sms, stream));
+      ctx->launches += 1;
+      return VODA_OK;
+    }
+    case VODA_ALGO_TIRESIAS:
+    case VODA_ALGO_ELASTIC_TIRESIAS: {
+      if (tiresias_smem_bytes(a, nullptr) > 220 * 1024)
+        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
+      CU(launch_tiresias(a, ctx->sms, stream));
+      ctx->launches += 1;
+      return VODA_OK;
+    }
+    case VODA_ALGO_AFSL: {
+      if (afsl_smem_bytes(a) > 220 * 1024)
+        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
+      CU(launch_afsl(a, ctx->sms, stream));
+      ctx->launches += 1;
+      return VODA_OK;
+    }
     default:
       return fail(ctx, VODA_E_UNSUPPORTED, "policy kernel not built into this library");
   }

@@ -1,3 +1,4 @@
 """Which reference policies have a CUDA kernel in this build (names of
 NewAlgorithmFactory, pkg/algorithm/types.go:26-47)."""
-SUPPORTED_ALGOS = ("FfDLOptimizer",)
+SUPPORTED_ALGOS = ("FIFO", "ElasticFIFO", "SRJF", "ElasticSRJF", "Tiresias", "ElasticTiresias",
+                   "FfDLOptimizer", "AFS-L")
