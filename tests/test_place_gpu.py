@@ -1,0 +1,80 @@
+"""GPU parity of the placement kernel (voda_place: bestFit + score + munkres + rename) against
+the CPU restatement, through the C ABI."""
+import numpy as np
+import pytest
+
+from helpers import load_kats, place_batch_from
+from vodascheduler_b200 import synth
+
+pytestmark = pytest.mark.gpu
+KATS = load_kats()
+
+
+def _same(pb, got, ref):
+    assert np.array_equal(got.status[:pb.rounds], ref.status[:pb.rounds])
+    for r in range(pb.rounds):
+        if ref.status[r] != 0:
+            continue
+        n0, n1 = int(pb.node_off[r]), int(pb.node_off[r + 1])
+        e0 = int(pb.req_off[r]) + n0
+        c = int(ref.lay_cnt[r])
+        assert got.lay_cnt[r] == c
+        for name in ("lay_node", "lay_job", "lay_workers"):
+            assert np.array_equal(getattr(got, name)[e0:e0 + c], getattr(ref, name)[e0:e0 + c]), (r, name)
+        assert np.array_equal(got.free_slots[n0:n1], ref.free_slots[n0:n1]), r
+        assert np.array_equal(got.phys_of_logical[n0:n1], ref.phys_of_logical[n0:n1]), r
+        assert got.score[r] == ref.score[r] and got.cross[r] == ref.cross[r]
+
+
+@pytest.mark.parametrize("kat", KATS["bestfit"], ids=lambda k: f"KAT-{k['kat']}")
+def test_bestfit_kat(ctx, kat):
+    pb = place_batch_from([dict(nodes=kat["nodes"], requests=kat["requests"])])
+    out = ctx.place(pb)
+    assert out.status[0] == kat["status"]
+    if kat["layout"] is not None:
+        c = int(out.lay_cnt[0])
+        got = [[int(out.lay_node[t]), int(out.lay_job[t]), int(out.lay_workers[t])] for t in range(c)]
+        assert got == kat["layout"]
+        assert out.free_slots[:len(kat["nodes"])].tolist() == kat["free"]
+
+
+@pytest.mark.parametrize("nodes,slots,jobs,load", [(4, 4, 6, 0.9), (16, 8, 30, 0.85), (37, 8, 70, 0.95),
+                                                   (128, 8, 200, 0.85), (128, 8, 400, 1.2)])
+def test_random_rounds(ctx, oracle, nodes, slots, jobs, load):
+    pb = synth.place_batch(rounds=12, nodes=nodes, slots=slots, jobs_per_round=jobs, load=load)
+    _same(pb, ctx.place(pb), oracle.place(pb, threads=8))
+
+
+def test_oversubscribed_and_quirks(ctx, oracle):
+    """Requests beyond the cluster: split jobs (Q11 over-assignment), early return when no slot
+    is left, and the never-ending loop (Q12 -> VODA_ST_NONTERMINATING)."""
+    rounds = [
+        dict(nodes=[8, 8], requests=[6, 6, 4], prev=[[(0, 6)], [(1, 6), (2, 2)]]),
+        dict(nodes=[8, 8], requests=[10, 3]),
+        dict(nodes=[8, 8], requests=[16, 1]),
+        dict(nodes=[4, 4, 4], requests=[5, 5, 2], prev=[[(0, 4)], [(0, 1), (1, 3)], [(2, 2)]]),
+        dict(nodes=[2, 2, 2, 2], requests=[0, 3, 0, 1, 1, 1], prev=[[(1, 2)], [(3, 1)], [], [(5, 1)]]),
+        dict(nodes=[], requests=[1, 2]),
+        dict(nodes=[8], requests=[]),
+        dict(nodes=[0, 0], requests=[1]),
+    ]
+    pb = place_batch_from(rounds)
+    got, ref = ctx.place(pb), oracle.place(pb)
+    _same(pb, got, ref)
+    assert 7 in ref.status[:len(rounds)].tolist()
+
+
+def test_ragged_batch(ctx, oracle):
+    rng = np.random.default_rng(5)
+    rounds = []
+    for _ in range(60):
+        n = int(rng.integers(1, 20))
+        m = int(rng.integers(0, 30))
+        nodes = [int(rng.integers(1, 9)) for _ in range(n)]
+        req = [int(rng.integers(0, 7)) for _ in range(m)]
+        prev = [[(int(rng.integers(0, max(1, m))), int(rng.integers(1, 4))) for _ in range(int(rng.integers(0, 3)))]
+                if m else [] for _ in range(n)]
+        prev = [list({j: (j, w) for j, w in p}.values()) for p in prev]  # one entry per job per node
+        rounds.append(dict(nodes=nodes, requests=req, prev=prev))
+    pb = place_batch_from(rounds)
+    _same(pb, ctx.place(pb), oracle.place(pb))

@@ -403,17 +403,172 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
   return VODA_OK;
 }
 
-int voda_munkres_max(voda_ctx* ctx, int32_t, int32_t, const int64_t*, int32_t*, int32_t*) {
-  return fail(ctx, VODA_E_UNSUPPORTED, "munkres kernel not built into this library");
+int voda_munkres_max_dev(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t* d_A, int32_t* d_out,
+                         int32_t* d_status) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  if (n < 0 || batch < 0) return fail(ctx, VODA_E_INVALID, "negative size");
+  if (n > 128) return fail(ctx, VODA_E_UNSUPPORTED, "munkres: n > 128 does not fit one CTA's shared memory");
+  if (batch == 0) return VODA_OK;
+  if (!d_status || (n > 0 && (!d_A || !d_out))) return fail(ctx, VODA_E_INVALID, "null buffer");
+  CU(cudaSetDevice(ctx->device));
+  if (n == 0) {  // NewMatrix(0): nothing to assign
+    CU(cudaMemsetAsync(d_status, 0, 4 * (size_t)batch, ctx->stream));
+    return VODA_OK;
+  }
+  int rc = ensure(ctx, ctx->scratch, munkres_scratch_bytes(batch), ctx->stream);
+  if (rc) return rc;
+  int launched = 0;
+  CU(launch_munkres(n, batch, d_A, d_out, d_status, ctx->scratch.p, ctx->sms, ctx->stream, &launched));
+  ctx->launches += launched;
+  return VODA_OK;
 }
-int voda_munkres_max_dev(voda_ctx* ctx, int32_t, int32_t, const int64_t*, int32_t*, int32_t*) {
-  return fail(ctx, VODA_E_UNSUPPORTED, "munkres kernel not built into this library");
+
+int voda_munkres_max(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t* A, int32_t* out, int32_t* status) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  if (n < 0 || batch < 0) return fail(ctx, VODA_E_INVALID, "negative size");
+  if (n > 128) return fail(ctx, VODA_E_UNSUPPORTED, "munkres: n > 128 does not fit one CTA's shared memory");
+  if (batch == 0) return VODA_OK;
+  if (!status || (n > 0 && (!A || !out))) return fail(ctx, VODA_E_INVALID, "null buffer");
+  if (n == 0) {
+    for (int b = 0; b < batch; b++) status[b] = VODA_ST_OK;
+    return VODA_OK;
+  }
+  CU(cudaSetDevice(ctx->device));
+  const size_t per = (size_t)n * n * 8;
+  // chunks big enough to occupy every SM (16 matrices per SM), at least ~8 MiB
+  size_t per_chunk = std::max<size_t>((size_t)ctx->sms * 16, (8u << 20) / per + 1);
+  if (per_chunk > (size_t)batch) per_chunk = (size_t)batch;
+  for (size_t c = 0, b0 = 0; b0 < (size_t)batch; c++, b0 += per_chunk) {
+    const size_t nb = std::min(per_chunk, (size_t)batch - b0);
+    const int slot = (int)(c & 1);
+    cudaStream_t s = ctx->pipe[slot];
+    const size_t o_A = 0, o_out = align256(per * nb), o_st = o_out + align256(4 * nb * n),
+                 o_need = o_st + align256(4 * nb), total = o_need + munkres_scratch_bytes((int)nb);
+    int rc = ensure(ctx, ctx->stage[slot], total, s);
+    if (rc) return rc;
+    char* base = (char*)ctx->stage[slot].p;
+    CU(cudaMemcpyAsync(base + o_A, A + b0 * (size_t)n * n, per * nb, cudaMemcpyHostToDevice, s));
+    int launched = 0;
+    CU(launch_munkres(n, (int)nb, (const int64_t*)(base + o_A), (int32_t*)(base + o_out), (int32_t*)(base + o_st),
+                      base + o_need, ctx->sms, s, &launched));
+    ctx->launches += launched;
+    CU(cudaMemcpyAsync(out + b0 * n, base + o_out, 4 * nb * n, cudaMemcpyDeviceToHost, s));
+    CU(cudaMemcpyAsync(status + b0, base + o_st, 4 * nb, cudaMemcpyDeviceToHost, s));
+  }
+  CU(cudaStreamSynchronize(ctx->pipe[0]));
+  CU(cudaStreamSynchronize(ctx->pipe[1]));
+  return VODA_OK;
 }
-int voda_place(voda_ctx* ctx, const voda_place_batch*, const voda_place_out*) {
-  return fail(ctx, VODA_E_UNSUPPORTED, "placement kernel not built into this library");
+
+static int check_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  if (!b || !o) return fail(ctx, VODA_E_INVALID, "null batch / out");
+  if (b->rounds < 0) return fail(ctx, VODA_E_INVALID, "negative round count");
+  if (b->rounds > 0 && (!b->node_off || !b->req_off || !b->prev_off || !o->status || !o->lay_cnt || !o->score || !o->cross))
+    return fail(ctx, VODA_E_INVALID, "null array");
+  return VODA_OK;
 }
-int voda_place_dev(voda_ctx* ctx, const voda_place_batch*, const voda_place_out*) {
-  return fail(ctx, VODA_E_UNSUPPORTED, "placement kernel not built into this library");
+
+static PlaceArgs make_place_args(const voda_place_batch* b, const voda_place_out* o) {
+  PlaceArgs a{};
+  a.rounds = b->rounds;
+  a.node_off = b->node_off; a.node_slots = b->node_slots; a.req_off = b->req_off; a.req_workers = b->req_workers;
+  a.prev_off = b->prev_off; a.prev_job = b->prev_job; a.prev_workers = b->prev_workers;
+  a.max_nodes = b->max_nodes; a.max_requests = b->max_requests;
+  a.phys_of_logical = o->phys_of_logical; a.free_slots = o->free_slots; a.lay_cnt = o->lay_cnt;
+  a.lay_node = o->lay_node; a.lay_job = o->lay_job; a.lay_workers = o->lay_workers;
+  a.score = reinterpret_cast<long long*>(o->score); a.cross = o->cross; a.status = o->status;
+  return a;
+}
+
+static int dispatch_place(voda_ctx* ctx, const PlaceArgs& a, cudaStream_t stream) {
+  if (a.rounds == 0) return VODA_OK;
+  if (a.max_nodes > 128) return fail(ctx, VODA_E_UNSUPPORTED, "placement: more than 128 nodes per round");
+  if (place_smem_bytes(a) > 220 * 1024)
+    return fail(ctx, VODA_E_UNSUPPORTED, "placement: too many requests per round for one CTA's shared memory");
+  CU(launch_place(a, ctx->sms, stream));
+  ctx->launches += 1;
+  return VODA_OK;
+}
+
+int voda_place_dev(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o) {
+  int rc = check_place(ctx, b, o);
+  if (rc) return rc;
+  if (b->max_nodes <= 0 || b->max_requests < 0)
+    return fail(ctx, VODA_E_INVALID, "voda_place_dev needs max_nodes / max_requests declared");
+  CU(cudaSetDevice(ctx->device));
+  PlaceArgs a = make_place_args(b, o);
+  if (a.max_requests < 1) a.max_requests = 1;
+  return dispatch_place(ctx, a, ctx->stream);
+}
+
+int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o) {
+  int rc = check_place(ctx, b, o);
+  if (rc) return rc;
+  const int R = b->rounds;
+  if (R == 0) return VODA_OK;
+  CU(cudaSetDevice(ctx->device));
+  const int nodes = b->node_off[R], reqs = b->req_off[R], prevs = b->prev_off[nodes];
+  int max_nodes = b->max_nodes, max_req = b->max_requests;
+  if (max_nodes <= 0 || max_req <= 0) {
+    int mn = 0, mr = 0;
+    for (int r = 0; r < R; r++) {
+      mn = std::max(mn, b->node_off[r + 1] - b->node_off[r]);
+      mr = std::max(mr, b->req_off[r + 1] - b->req_off[r]);
+    }
+    if (max_nodes <= 0) max_nodes = std::max(mn, 1);
+    if (max_req <= 0) max_req = std::max(mr, 1);
+  }
+  // placement batches are small (a few KB per round): one staged copy, one kernel
+  cudaStream_t s = ctx->pipe[0];
+  size_t pos = 0;
+  auto carve = [&](size_t bytes) { size_t at = pos; pos += align256(bytes ? bytes : 1); return at; };
+  const size_t cap = (size_t)nodes + (size_t)reqs;
+  const size_t i_no = carve(4 * (size_t)(R + 1)), i_ns = carve(4 * (size_t)nodes), i_ro = carve(4 * (size_t)(R + 1)),
+               i_rw = carve(4 * (size_t)reqs), i_po = carve(4 * (size_t)(nodes + 1)), i_pj = carve(4 * (size_t)prevs),
+               i_pw = carve(4 * (size_t)prevs);
+  const size_t o_ph = carve(4 * (size_t)nodes), o_fr = carve(4 * (size_t)nodes), o_lc = carve(4 * (size_t)R),
+               o_ln = carve(4 * cap), o_lj = carve(4 * cap), o_lw = carve(4 * cap), o_sc = carve(8 * (size_t)R),
+               o_cr = carve(4 * (size_t)R), o_st = carve(4 * (size_t)R);
+  rc = ensure(ctx, ctx->stage[0], pos, s);
+  if (rc) return rc;
+  char* base = (char*)ctx->stage[0].p;
+  auto h2d = [&](size_t at, const void* src, size_t bytes) -> cudaError_t {
+    return bytes ? cudaMemcpyAsync(base + at, src, bytes, cudaMemcpyHostToDevice, s) : cudaSuccess;
+  };
+  CU(h2d(i_no, b->node_off, 4 * (size_t)(R + 1)));
+  CU(h2d(i_ns, b->node_slots, 4 * (size_t)nodes));
+  CU(h2d(i_ro, b->req_off, 4 * (size_t)(R + 1)));
+  CU(h2d(i_rw, b->req_workers, 4 * (size_t)reqs));
+  CU(h2d(i_po, b->prev_off, 4 * (size_t)(nodes + 1)));
+  CU(h2d(i_pj, b->prev_job, 4 * (size_t)prevs));
+  CU(h2d(i_pw, b->prev_workers, 4 * (size_t)prevs));
+  PlaceArgs a{};
+  a.rounds = R;
+  a.node_off = (const int32_t*)(base + i_no); a.node_slots = (const int32_t*)(base + i_ns);
+  a.req_off = (const int32_t*)(base + i_ro); a.req_workers = (const int32_t*)(base + i_rw);
+  a.prev_off = (const int32_t*)(base + i_po); a.prev_job = (const int32_t*)(base + i_pj);
+  a.prev_workers = (const int32_t*)(base + i_pw);
+  a.max_nodes = max_nodes; a.max_requests = max_req;
+  a.phys_of_logical = (int32_t*)(base + o_ph); a.free_slots = (int32_t*)(base + o_fr); a.lay_cnt = (int32_t*)(base + o_lc);
+  a.lay_node = (int32_t*)(base + o_ln); a.lay_job = (int32_t*)(base + o_lj); a.lay_workers = (int32_t*)(base + o_lw);
+  a.score = (long long*)(base + o_sc); a.cross = (int32_t*)(base + o_cr); a.status = (int32_t*)(base + o_st);
+  rc = dispatch_place(ctx, a, s);
+  if (rc) return rc;
+  auto d2h = [&](void* dst, size_t at, size_t bytes) -> cudaError_t {
+    return (bytes && dst) ? cudaMemcpyAsync(dst, base + at, bytes, cudaMemcpyDeviceToHost, s) : cudaSuccess;
+  };
+  CU(d2h(o->phys_of_logical, o_ph, 4 * (size_t)nodes));
+  CU(d2h(o->free_slots, o_fr, 4 * (size_t)nodes));
+  CU(d2h(o->lay_cnt, o_lc, 4 * (size_t)R));
+  CU(d2h(o->lay_node, o_ln, 4 * cap));
+  CU(d2h(o->lay_job, o_lj, 4 * cap));
+  CU(d2h(o->lay_workers, o_lw, 4 * cap));
+  CU(d2h(o->score, o_sc, 8 * (size_t)R));
+  CU(d2h(o->cross, o_cr, 4 * (size_t)R));
+  CU(d2h(o->status, o_st, 4 * (size_t)R));
+  CU(cudaStreamSynchronize(s));
+  return VODA_OK;
 }
 
 }  // extern "C"

@@ -39,6 +39,28 @@ struct AllocArgs {
   int32_t* out_status;
 };
 
+// Kernel-side view of a voda_place_batch + voda_place_out (device pointers).
+struct PlaceArgs {
+  int32_t rounds;
+  const int32_t* node_off;
+  const int32_t* node_slots;
+  const int32_t* req_off;
+  const int32_t* req_workers;
+  const int32_t* prev_off;
+  const int32_t* prev_job;
+  const int32_t* prev_workers;
+  int32_t max_nodes, max_requests;
+  int32_t* phys_of_logical;
+  int32_t* free_slots;
+  int32_t* lay_cnt;
+  int32_t* lay_node;
+  int32_t* lay_job;
+  int32_t* lay_workers;
+  long long* score;
+  int32_t* cross;
+  int32_t* status;
+};
+
 __host__ __device__ inline int next_pow2(int x) {
   int p = 1;
   while (p < x) p <<= 1;

@@ -26,4 +26,13 @@ cudaError_t launch_tiresias(const AllocArgs& a, int sms, cudaStream_t stream);
 size_t afsl_smem_bytes(const AllocArgs& a);
 cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream);
 
+// batched ComputeMunkresMax (munkres.cu)
+size_t munkres_scratch_bytes(int batch);
+cudaError_t launch_munkres(int n, int batch, const int64_t* A, int32_t* out, int32_t* status, void* scratch,
+                           int sms, cudaStream_t stream, int* launched);
+
+// bestFit + score + munkres placement rounds (place.cu)
+size_t place_smem_bytes(const PlaceArgs& a);
+cudaError_t launch_place(const PlaceArgs& a, int sms, cudaStream_t stream);
+
 }  // namespace voda

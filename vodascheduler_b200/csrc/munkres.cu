@@ -1,0 +1,154 @@
+// munkres.cu — batched ComputeMunkresMax (pkg/placement/placement_manager.go:505-512; module
+// github.com/heyfey/munkres) : one warp-sized CTA per n x n int64 score matrix.
+//
+// The matrix is read once from HBM (coalesced 256-byte row segments), turned into
+// C[i][j] = rowmax_i - A[i][j] and parked in shared memory in the NARROWEST cell type that
+// holds every C value, because shared memory per matrix sets how many matrices an SM works on
+// at once (16 KB as uint8 -> 12 per SM; 128 KB as int64 -> 1 per SM).  The type is found by
+// trying: the uint8 kernel runs over the whole batch and marks the matrices whose range does
+// not fit; the uint16 / int32 / int64 kernels then pick up only what was marked (each is an
+// almost-empty launch when nothing was).  The solve itself is munkres.cuh.
+#include "kernels.h"
+#include "munkres.cuh"
+
+namespace voda {
+namespace {
+
+template <typename CellT>
+struct CellMax;
+template <> struct CellMax<uint8_t> { static constexpr long long v = 255; };
+template <> struct CellMax<uint16_t> { static constexpr long long v = 65535; };
+template <> struct CellMax<int32_t> { static constexpr long long v = 0x7fffffffLL; };
+template <> struct CellMax<int64_t> { static constexpr long long v = 0x7fffffffffffffffLL; };
+
+__device__ __forceinline__ long long warp_max_ll(long long v) {
+  for (int d = 16; d > 0; d >>= 1) {
+    long long o = __shfl_xor_sync(0xffffffffu, v, d);
+    v = o > v ? o : v;
+  }
+  return v;
+}
+
+template <typename CellT>
+__global__ void __launch_bounds__(32) munkres_kernel(int n, int batch, const int64_t* __restrict__ A,
+                                                     int32_t* __restrict__ out, int32_t* __restrict__ status,
+                                                     unsigned char* __restrict__ need, int level) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  using Pot = typename MunkresTypes<CellT>::Pot;
+  CellT* C = reinterpret_cast<CellT*>(smem_raw);
+  size_t off = ((size_t)n * n * sizeof(CellT) + 15) & ~(size_t)15;
+  MunkresSmem sm;
+  sm.ra = smem_raw + off; off += 128 * sizeof(Pot);
+  sm.starCol = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
+  sm.starRow = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
+  sm.primeCol = reinterpret_cast<short*>(smem_raw + off);
+  const int lane = threadIdx.x;
+  const unsigned full = 0xffffffffu;
+  const long long NEG = (long long)0x8000000000000000ULL;
+
+  for (int b = blockIdx.x; b < batch; b += gridDim.x) {
+    if (need[b] != level) continue;
+    const int64_t* M = A + (size_t)b * n * n;
+    uint32_t Z[4][4];
+#pragma unroll
+    for (int q = 0; q < 4; q++)
+#pragma unroll
+      for (int t = 0; t < 4; t++) Z[q][t] = 0;
+    bool overflow = false;
+    __syncwarp();
+    for (int l = 0; l < 32 && 4 * l < n; l++) {
+      // 4 rows x 4 column blocks in flight
+      long long v[4][4];
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int i = 4 * l + q;
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+          const int col = lane + 32 * t;
+          v[q][t] = (i < n && col < n) ? M[(size_t)i * n + col] : NEG;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int i = 4 * l + q;
+        if (i >= n) break;
+        long long mx = v[q][0];
+#pragma unroll
+        for (int t = 1; t < 4; t++) mx = v[q][t] > mx ? v[q][t] : mx;
+        mx = warp_max_ll(mx);
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+          const int col = lane + 32 * t;
+          const bool valid = col < n;
+          // rowmax - A: wraps only when the row's range exceeds int64, which no cell type
+          // here can hold either; such a matrix is out of the reference's domain too
+          const unsigned long long c = valid ? (unsigned long long)mx - (unsigned long long)v[q][t] : 0ull;
+          if (c > (unsigned long long)CellMax<CellT>::v) overflow = true;
+          if (valid) C[(size_t)i * n + col] = (CellT)c;
+          const unsigned bz = __ballot_sync(full, valid && c == 0);
+          if (lane == l) Z[q][t] = bz;
+        }
+      }
+    }
+    if (__any_sync(full, overflow)) {
+      if (level < 3) {
+        if (lane == 0) need[b] = (unsigned char)(level + 1);  // a wider kernel takes it
+      } else {  // a row's range exceeds int64: outside the reference's domain as well
+        for (int i = lane; i < n; i += 32) out[(size_t)b * n + i] = -1;
+        if (lane == 0) status[b] = VODA_ST_BOUND;
+      }
+      continue;
+    }
+    __syncwarp();
+    munkres_solve<CellT>(C, n, Z, sm);
+    for (int i = lane; i < n; i += 32) out[(size_t)b * n + i] = sm.starCol[i];
+    if (lane == 0) status[b] = VODA_ST_OK;
+    __syncwarp();
+  }
+}
+
+template <typename CellT>
+size_t munkres_smem(int n) {
+  using Pot = typename MunkresTypes<CellT>::Pot;
+  return (((size_t)n * n * sizeof(CellT) + 15) & ~(size_t)15) + 128 * sizeof(Pot) + 3 * 128 * sizeof(short) + 16;
+}
+
+template <typename CellT>
+cudaError_t launch_level(int n, int batch, const int64_t* A, int32_t* out, int32_t* status, unsigned char* need,
+                         int level, int sms, cudaStream_t stream) {
+  const size_t smem = munkres_smem<CellT>(n);
+  auto kern = munkres_kernel<CellT>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  int perSm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, 32, smem);
+  if (e != cudaSuccess) return e;
+  if (perSm < 1) perSm = 1;
+  int grid = sms * perSm;
+  if (batch < grid) grid = batch;
+  kern<<<grid, 32, smem, stream>>>(n, batch, A, out, status, need, level);
+  return cudaGetLastError();
+}
+
+}  // namespace
+
+size_t munkres_scratch_bytes(int batch) { return ((size_t)batch + 255) & ~(size_t)255; }
+
+// Enqueues memset + up to four kernels; returns the number of kernels launched in *launched.
+cudaError_t launch_munkres(int n, int batch, const int64_t* A, int32_t* out, int32_t* status, void* scratch,
+                           int sms, cudaStream_t stream, int* launched) {
+  unsigned char* need = static_cast<unsigned char*>(scratch);
+  cudaError_t e = cudaMemsetAsync(need, 0, (size_t)batch, stream);
+  if (e != cudaSuccess) return e;
+  *launched = 0;
+  if ((e = launch_level<uint8_t>(n, batch, A, out, status, need, 0, sms, stream)) != cudaSuccess) return e;
+  if ((e = launch_level<uint16_t>(n, batch, A, out, status, need, 1, sms, stream)) != cudaSuccess) return e;
+  if ((e = launch_level<int32_t>(n, batch, A, out, status, need, 2, sms, stream)) != cudaSuccess) return e;
+  if ((e = launch_level<int64_t>(n, batch, A, out, status, need, 3, sms, stream)) != cudaSuccess) return e;
+  *launched = 4;
+  return cudaSuccess;
+}
+
+}  // namespace voda

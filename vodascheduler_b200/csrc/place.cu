@@ -1,0 +1,318 @@
+// place.cu — the arithmetic core of PlacementManager.Place for a batch of rounds (sm_100a):
+//   bestFit            pkg/placement/placement_manager.go:415-487
+//   scoreCandidates    :525-544   M[logical r][physical c] = sum over jobs of r of
+//                                 (cand_c[job] <= pos_r[job] ? cand_c[job] : pos_r[job])
+//   ComputeMunkresMax  :505-507   (munkres.cuh)
+//   rename + score     :509-512
+// One CTA per round.  Warp 0 runs bestFit (a serial walk over the sorted requests; the two
+// node searches per step are warp reductions over (freeSlots, index) keys that keep the
+// reference's first-index tie-breaks), all threads build the n x n score matrix in shared
+// memory with atomics (a join of the new layout and the previous one on the job id), then
+// warp 0 solves the assignment in place.  Reference quirks kept: the last chunk of a split job
+// records the WHOLE request (Q11, :479) so freeSlots can go negative, and the loop that never
+// ends once a request meets a cluster without usable slots (Q12) is cut with
+// VODA_ST_NONTERMINATING.
+#include "kernels.h"
+#include "munkres.cuh"
+
+namespace voda {
+namespace {
+
+constexpr int kThreads = 128;
+constexpr int kMaxNodes = 128;
+constexpr int kLimit = 1 << 22;  // |freeSlots| * 128 must fit an int32 key
+
+struct PlaceSmem {
+  int32_t* M;        // [n*n] scores, then rowmax - score
+  int64_t* khi;      // [Mp] sort key (-workers)
+  int32_t* klo;      // [Mp] zeros
+  int* perm;         // [Mp]
+  int32_t* workers;  // [Mp]
+  int* jobHead;      // [Mp] first layout entry of a job, -1 if none
+  int32_t* eNode;    // [Mp + 128]
+  int32_t* eJob;
+  int32_t* eW;
+  int* eNext;
+  int32_t* rowmax;   // [128]
+  long long* red;    // [4]
+  MunkresSmem mk;
+};
+
+__global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  PlaceSmem sm;
+  {
+    unsigned char* p = smem_raw;
+    sm.M = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)a.max_nodes * a.max_nodes;
+    p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
+    sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Mp;
+    sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
+    sm.mk.ra = p; p += 8 * 128;
+    sm.klo = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Mp;
+    sm.perm = reinterpret_cast<int*>(p); p += 4 * (size_t)Mp;
+    sm.workers = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Mp;
+    sm.jobHead = reinterpret_cast<int*>(p); p += 4 * (size_t)Mp;
+    sm.eNode = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
+    sm.eJob = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
+    sm.eW = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
+    sm.eNext = reinterpret_cast<int*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
+    sm.rowmax = reinterpret_cast<int32_t*>(p); p += 4 * 128;
+    sm.mk.starCol = reinterpret_cast<short*>(p); p += 2 * 128;
+    sm.mk.starRow = reinterpret_cast<short*>(p); p += 2 * 128;
+    sm.mk.primeCol = reinterpret_cast<short*>(p);
+  }
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned full = 0xffffffffu;
+
+  for (int rd = blockIdx.x; rd < a.rounds; rd += gridDim.x) {
+    const int n0 = a.node_off[rd], n = a.node_off[rd + 1] - n0;
+    const int q0 = a.req_off[rd], m = a.req_off[rd + 1] - q0;
+    const int e0 = q0 + n0;
+    __syncthreads();
+    if (tid == 0) {
+      sm.red[0] = VODA_ST_OK;  // status
+      sm.red[1] = 0;           // entries
+      sm.red[2] = 0;           // cross
+    }
+    if (n <= 0) {  // no nodes: bestFit returns at once, size-0 matrix
+      if (tid == 0) {
+        a.lay_cnt[rd] = 0; a.score[rd] = 0; a.cross[rd] = 0; a.status[rd] = VODA_ST_OK;
+      }
+      continue;
+    }
+    if (n > a.max_nodes || n > kMaxNodes || m > a.max_requests) {
+      if (tid == 0) {
+        a.lay_cnt[rd] = 0; a.score[rd] = 0; a.cross[rd] = 0; a.status[rd] = VODA_ST_BOUND;
+      }
+      continue;
+    }
+    // requests sorted by numWorkers descending, stable (:422-424); the len(jobRequests)
+    // zero-valued leading entries of the reference (:416, Q10) never enter the loop body
+    int tooBig = 0;
+    for (int i = tid; i < m; i += kThreads) {
+      const int w = a.req_workers[q0 + i];
+      sm.workers[i] = w;
+      sm.khi[i] = -(int64_t)w;
+      sm.klo[i] = 0;
+      sm.jobHead[i] = -1;
+      tooBig |= (w >= kLimit);
+    }
+    for (int i = tid; i < n; i += kThreads) {
+      const int s = a.node_slots[n0 + i];
+      tooBig |= (s >= kLimit || s <= -kLimit);
+    }
+    for (int x = tid; x < n * n; x += kThreads) sm.M[x] = 0;
+    if (__syncthreads_or(tooBig)) {
+      if (tid == 0) {
+        a.lay_cnt[rd] = 0; a.score[rd] = 0; a.cross[rd] = 0; a.status[rd] = VODA_ST_BOUND;
+      }
+      continue;
+    }
+    block_argsort(sm.khi, sm.klo, sm.perm, m, next_pow2(m > 0 ? m : 1));
+
+    // ---- bestFit (warp 0) -------------------------------------------------------------
+    if (warp == 0) {
+      int fr[4];
+      bool valid[4];
+      long long total = 0;
+#pragma unroll
+      for (int q = 0; q < 4; q++) {
+        const int i = lane + 32 * q;
+        valid[q] = i < n;
+        fr[q] = valid[q] ? a.node_slots[n0 + i] : 0;  // NewNodeState("TBD", totalSlots) (:317-320)
+        total += fr[q];
+      }
+      for (int d = 16; d > 0; d >>= 1) total += __shfl_xor_sync(full, total, d);
+      int cnt = 0, cross = 0, status = VODA_ST_OK;
+      bool stop = false;
+      for (int t = 0; t < m && !stop; t++) {
+        const int job = sm.perm[t];
+        const int w = sm.workers[job];
+        int requested = w;
+        int tail = -1;
+        while (requested > 0) {
+          if (total == 0) {  // :455-457 return
+            stop = true;
+            break;
+          }
+          int keyb = 0x7fffffff, keym = (int)0x80000000;
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            if (valid[q]) {
+              const int i = lane + 32 * q;
+              if (fr[q] >= requested) keyb = min(keyb, fr[q] * 128 + i);
+              keym = max(keym, fr[q] * 128 + (127 - i));
+            }
+          }
+          const int kb = __reduce_min_sync(full, keyb);
+          int node, give;
+          if (kb == 0x7fffffff) {  // no node fits: take everything from the fullest one (:472-477)
+            const int km = __reduce_max_sync(full, keym);
+            node = 127 - (km & 127);
+            give = km >> 7;
+            if (give == 0) {  // the state can never change again (Q12)
+              status = VODA_ST_NONTERMINATING;
+              stop = true;
+              break;
+            }
+            requested -= give;
+            total -= give;
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+              if (lane + 32 * q == node) fr[q] = 0;
+            cross++;
+          } else {  // best fit; records and subtracts the WHOLE request (:479-482)
+            node = kb & 127;
+            give = w;
+            requested -= w;
+            total -= w;
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+              if (lane + 32 * q == node) fr[q] -= w;
+          }
+          if (lane == 0) {
+            sm.eNode[cnt] = node;
+            sm.eJob[cnt] = job;
+            sm.eW[cnt] = give;
+            sm.eNext[cnt] = -1;
+            if (tail < 0) sm.jobHead[job] = cnt; else sm.eNext[tail] = cnt;
+          }
+          tail = cnt;
+          cnt++;
+        }
+      }
+#pragma unroll
+      for (int q = 0; q < 4; q++)
+        if (valid[q]) a.free_slots[n0 + lane + 32 * q] = fr[q];
+      if (lane == 0) {
+        sm.red[0] = status;
+        sm.red[1] = cnt;
+        sm.red[2] = cross;
+      }
+    }
+    __syncthreads();
+    const int status = (int)sm.red[0];
+    const int cnt = (int)sm.red[1];
+    if (status != VODA_ST_OK) {
+      if (tid == 0) {
+        a.lay_cnt[rd] = 0; a.score[rd] = 0; a.cross[rd] = 0; a.status[rd] = status;
+      }
+      continue;
+    }
+    for (int e = tid; e < cnt; e += kThreads) {
+      a.lay_node[e0 + e] = sm.eNode[e];
+      a.lay_job[e0 + e] = sm.eJob[e];
+      a.lay_workers[e0 + e] = sm.eW[e];
+    }
+    // ---- score matrix: join previous (physical) entries with the new layout on the job ----
+    const int p0 = a.prev_off[n0], p1 = a.prev_off[n0 + n];
+    for (int pe = p0 + tid; pe < p1; pe += kThreads) {
+      const int job = a.prev_job[pe];
+      if (job < 0 || job >= m) continue;  // a job that is not requested cannot be in the new layout
+      const int cw = a.prev_workers[pe];
+      // physical node of this entry: the node whose [prev_off) range holds pe
+      int lo = 0, hi = n - 1;
+      while (lo < hi) {
+        const int mid = (lo + hi + 1) >> 1;
+        if (a.prev_off[n0 + mid] <= pe) lo = mid; else hi = mid - 1;
+      }
+      const int c = lo;
+      for (int e = sm.jobHead[job]; e >= 0; e = sm.eNext[e]) {
+        const int w = sm.eW[e];
+        if (w < 0) continue;  // handled below for every column
+        atomicAdd(&sm.M[sm.eNode[e] * n + c], cw <= w ? cw : w);
+      }
+    }
+    // rare: a layout entry with a negative count (reference quirk) contributes to EVERY
+    // column, because an absent candidate reads 0 and 0 <= negative is false (:537-541)
+    for (int e = tid; e < cnt; e += kThreads) {
+      const int w = sm.eW[e];
+      if (w >= 0) continue;
+      const int job = sm.eJob[e];
+      for (int c = 0; c < n; c++) {
+        int cand = 0;
+        for (int pe = a.prev_off[n0 + c]; pe < a.prev_off[n0 + c + 1]; pe++)
+          if (a.prev_job[pe] == job) cand = a.prev_workers[pe];
+        atomicAdd(&sm.M[sm.eNode[e] * n + c], cand <= w ? cand : w);
+      }
+    }
+    __syncthreads();
+    // ---- ComputeMunkresMax on M (warp 0), then rename + total score ------------------------
+    if (warp == 0) {
+      uint32_t Z[4][4];
+#pragma unroll
+      for (int q = 0; q < 4; q++)
+#pragma unroll
+        for (int t = 0; t < 4; t++) Z[q][t] = 0;
+      for (int l = 0; l < 32 && 4 * l < n; l++) {
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const int i = 4 * l + q;
+          if (i >= n) break;
+          int v[4];
+          int mx = (int)0x80000000;
+#pragma unroll
+          for (int t = 0; t < 4; t++) {
+            const int col = lane + 32 * t;
+            v[t] = col < n ? sm.M[i * n + col] : (int)0x80000000;
+            mx = max(mx, v[t]);
+          }
+          mx = __reduce_max_sync(full, mx);
+          if (lane == 0) sm.rowmax[i] = mx;
+#pragma unroll
+          for (int t = 0; t < 4; t++) {
+            const int col = lane + 32 * t;
+            const bool ok = col < n;
+            const int c = ok ? mx - v[t] : 1;
+            if (ok) sm.M[i * n + col] = c;
+            const unsigned bz = __ballot_sync(full, ok && c == 0);
+            if (lane == l) Z[q][t] = bz;
+          }
+        }
+      }
+      __syncwarp();
+      munkres_solve<int32_t>(sm.M, n, Z, sm.mk);
+      long long sc = 0;
+      for (int i = lane; i < n; i += 32) {
+        const int col = sm.mk.starCol[i];
+        a.phys_of_logical[n0 + i] = col;
+        sc += (long long)sm.rowmax[i] - (long long)sm.M[i * n + col];
+      }
+      for (int d = 16; d > 0; d >>= 1) sc += __shfl_xor_sync(full, sc, d);
+      if (lane == 0) {
+        a.score[rd] = sc;
+        a.lay_cnt[rd] = cnt;
+        a.cross[rd] = (int)sm.red[2];
+        a.status[rd] = VODA_ST_OK;
+      }
+    }
+  }
+}
+
+size_t place_smem(int maxNodes, int Mp) {
+  return 4 * (size_t)maxNodes * maxNodes + 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 8 * 128 +
+         4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 64;
+}
+
+}  // namespace
+
+size_t place_smem_bytes(const PlaceArgs& a) { return place_smem(a.max_nodes, next_pow2(a.max_requests > 0 ? a.max_requests : 1)); }
+
+cudaError_t launch_place(const PlaceArgs& a, int sms, cudaStream_t stream) {
+  const int Mp = next_pow2(a.max_requests > 0 ? a.max_requests : 1);
+  const size_t smem = place_smem(a.max_nodes, Mp);
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  int perSm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, place_kernel, kThreads, smem);
+  if (e != cudaSuccess) return e;
+  if (perSm < 1) perSm = 1;
+  int grid = sms * perSm;
+  if (a.rounds < grid) grid = a.rounds;
+  place_kernel<<<grid, kThreads, smem, stream>>>(a, Mp);
+  return cudaGetLastError();
+}
+
+}  // namespace voda
