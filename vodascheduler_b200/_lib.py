@@ -14,7 +14,8 @@ from . import _abi
 from .batch import AllocBatch, PlaceBatch, PlaceOut
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "libvoda_accel.so")
+# VODA_ACCEL_LIB lets a profiling run point at an experimental build of the same library
+_SO = os.environ.get("VODA_ACCEL_LIB") or os.path.join(_HERE, "libvoda_accel.so")
 
 
 class EngineError(RuntimeError):

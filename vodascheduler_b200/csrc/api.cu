@@ -138,14 +138,20 @@ int dispatch_alloc(voda_ctx* ctx, const AllocArgs& a, DevBuf& scratch, cudaStrea
   if (a.rounds == 0) return VODA_OK;
   switch (a.algo) {
     case VODA_ALGO_FFDL_OPTIMIZER: {
-      const int grid = ffdl_grid(ctx->sms, a.rounds);
       if (ffdl_smem_bytes(a) > 200 * 1024)
         return fail(ctx, VODA_E_UNSUPPORTED, "FfDL: total_gpu / jobs too large for one CTA's shared memory");
-      const size_t need = ffdl_scratch_bytes(a, grid);
-      int rc = ensure(ctx, scratch, need, stream);
+      // every round keeps its SOL slab until the backtrack kernel has read it: cap the scratch
+      // at 8 GiB and walk larger batches in sub-batches (two launches each)
+      const size_t per = (ffdl_scratch_per_round(a) + 255) & ~(size_t)255;
+      const size_t budget = (size_t)8 << 30;
+      int sub = (int)std::min<size_t>((size_t)a.rounds, std::max<size_t>(1, budget / per));
+      int rc = ensure(ctx, scratch, per * (size_t)sub, stream);
       if (rc) return rc;
-      CU(launch_ffdl(a, grid, scratch.p, need, stream));
-      ctx->launches += 1;
+      for (int r0 = 0; r0 < a.rounds; r0 += sub) {
+        const int count = std::min(sub, a.rounds - r0);
+        CU(launch_ffdl(a, r0, count, ctx->sms, scratch.p, stream));
+        ctx->launches += 2;
+      }
       return VODA_OK;
     }
     case VODA_ALGO_FIFO:

@@ -10,9 +10,11 @@
 //      cells and slides an 8-register window of row j-1 over g, so a block of 4 g-steps x 4
 //      cells costs one LDS.128 of P and one LDS.128 (broadcast) of S for 64 add/compare/select
 //      groups.  The argmax is per cell; no cross-thread reduction is needed.
-//   4. SOL[j][k] (the chosen g) is streamed to a per-CTA slab of global scratch (uint8 when
+//   4. SOL[j][k] (the chosen g) is streamed to the round's slab of global scratch (uint8 when
 //      the round's largest g fits, else uint16); it is written once and only J cells are read
-//      back by the backtrack (:116-125).
+//      back by the backtrack (:116-125), which is a SECOND kernel (one warp per round): the
+//      chase is a chain of J dependent loads, and inside the DP kernel it would leave the CTA
+//      idle for a fifth of its life; side by side over thousands of rounds it costs nothing.
 //   5. P[J][K] <= 0 -> "infeasible" (:109-114); deferred validateResult (:42).
 //
 // float32 evaluation order: p = S_j[g] + P[j-1][k-g] is a single rounded add (-fmad=false;
@@ -26,7 +28,18 @@ namespace voda {
 
 namespace {
 
-constexpr int kThreads = 64;
+#ifndef VODA_FFDL_THREADS
+#define VODA_FFDL_THREADS 64
+#endif
+#ifndef VODA_FFDL_CELLS
+#define VODA_FFDL_CELLS 8
+#endif
+#ifndef VODA_FFDL_MINBLOCKS
+#define VODA_FFDL_MINBLOCKS 1
+#endif
+// 64 threads x 8 cells (two tiles per thread at K = 1024) measured best on B200 among
+// {32,64,128} x {4,8,16,32}; see profiles/r1_ffdl_shape_sweep.txt
+constexpr int kThreads = VODA_FFDL_THREADS;
 
 struct FfdlSmem {
   float4* rowA;      // [G4]  row buffers, group q = P[4q-3 .. 4q]
@@ -51,20 +64,21 @@ __device__ __forceinline__ float4 ld_group(const float4* row, int q) {
 // Instruction mix matters here (the loop is bound by the ALU pipe): the running maximum is an
 // FMNMX, the "did it win" bit an FSET (1.0f / 0.0f), and the winning g is NOT tracked with a
 // select per step: the win bits are shifted into a float accumulator with an FFMA
-// (acc = acc*2 + bit, exact below 2^24), i.e. on the FMA pipe, and the last win is decoded
-// once per flush.  fmaxf(best, p) equals the reference's strict-'>' select for every non-NaN
-// input (equal values are interchangeable; a NaN p never replaces best in either form).
+// (acc = acc/2 + bit, i.e. on the FMA pipe; exact for up to 23 steps), so the exponent of acc
+// says how many steps ago the LAST win happened, and it is decoded once per flush.
+// fmaxf(best, p) equals the reference's strict-'>' select for every non-NaN input (equal
+// values are interchangeable; a NaN p never replaces best in either form).
 #define VODA_CELL(c, s)                              \
   {                                                  \
     const float p = sv[s] + v[3 + (c) - (s)];        \
     const float t = (p > best[c]) ? 1.0f : 0.0f;     \
     best[c] = fmaxf(best[c], p);                     \
-    acc[c] = fmaf(acc[c], 2.0f, t);                  \
+    acc[c] = fmaf(acc[c], 0.5f, t);                  \
   }
 
-constexpr int kCells = 16;              // adjacent cells per thread
+constexpr int kCells = VODA_FFDL_CELLS;  // adjacent cells per thread
 constexpr int kGroups = kCells / 4 + 1;  // float4 groups of row j-1 in the sliding window
-constexpr int kFlushBlocks = 6;          // 6 blocks x 4 g-steps = 24 win bits per accumulator flush
+constexpr int kFlushBlocks = 5;          // 5 blocks x 4 g-steps = 20 win bits per accumulator flush
 
 // One DP row for column tile `tq` (cells k = kCells*tq+1 .. kCells*tq+kCells).
 // Row storage: group q = P[4q-3 .. 4q].  For the block of g = 4m+1 .. 4m+4 the cells need
@@ -109,12 +123,13 @@ __device__ __forceinline__ void ffdl_row_tile(const float4* __restrict__ prev, f
     for (int i = kGroups - 1; i > 0; i--) grp[i] = grp[i - 1];
     grp[0] = ld_group(prev, qtop - m - 1);
     if (++sinceFlush == kFlushBlocks || m == nblk - 1) {
-      // decode the last win of the flushed span: bit b (from the LSB) is g = gEnd - b
+      // decode the last win of the flushed span: acc in [2^-d, 2^(1-d)) <=> it happened d
+      // steps before the last one of the span, i.e. at g = gEnd - d
       const int gEnd = 4 * m + 4;
 #pragma unroll
       for (int c = 0; c < kCells; c++) {
-        const int bits = __float2int_rz(acc[c]);
-        if (bits) bg[c] = gEnd - (__ffs(bits) - 1);
+        const int e = __float_as_int(acc[c]) >> 23;  // biased exponent (acc >= 0)
+        if (e) bg[c] = gEnd - 127 + e;
         acc[c] = 0.0f;
       }
       sinceFlush = 0;
@@ -138,19 +153,24 @@ __device__ __forceinline__ void ffdl_row_tile(const float4* __restrict__ prev, f
 #pragma unroll
   for (int i = 0; i < kCells / 4; i++)
     cur[qtop + 1 + i] = make_float4(best[4 * i], best[4 * i + 1], best[4 * i + 2], best[4 * i + 3]);
+  // SOL entries of the tile, packed and stored with the widest aligned vector store
+  constexpr int kWords = kCells * (int)sizeof(SolT) / 4;
+  uint32_t w[kWords];
   if (sizeof(SolT) == 1) {
-    uint32_t w[kCells / 4];
 #pragma unroll
-    for (int i = 0; i < kCells / 4; i++)
+    for (int i = 0; i < kWords; i++)
       w[i] = (uint32_t)bg[4 * i] | ((uint32_t)bg[4 * i + 1] << 8) | ((uint32_t)bg[4 * i + 2] << 16) |
              ((uint32_t)bg[4 * i + 3] << 24);
-    reinterpret_cast<uint4*>(solrow)[tq] = make_uint4(w[0], w[1], w[2], w[3]);
   } else {
-    uint32_t w[kCells / 2];
 #pragma unroll
-    for (int i = 0; i < kCells / 2; i++) w[i] = (uint32_t)bg[2 * i] | ((uint32_t)bg[2 * i + 1] << 16);
-    reinterpret_cast<uint4*>(solrow)[2 * tq] = make_uint4(w[0], w[1], w[2], w[3]);
-    reinterpret_cast<uint4*>(solrow)[2 * tq + 1] = make_uint4(w[4], w[5], w[6], w[7]);
+    for (int i = 0; i < kWords; i++) w[i] = (uint32_t)bg[2 * i] | ((uint32_t)bg[2 * i + 1] << 16);
+  }
+  uint32_t* dst = reinterpret_cast<uint32_t*>(solrow) + (size_t)tq * kWords;
+  if (kWords >= 4) {
+#pragma unroll
+    for (int i = 0; i < kWords; i += 4) *reinterpret_cast<uint4*>(dst + i) = make_uint4(w[i], w[i + 1], w[i + 2], w[i + 3]);
+  } else {
+    *reinterpret_cast<uint2*>(dst) = make_uint2(w[0], w[1]);
   }
 }
 
@@ -211,8 +231,26 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, 
   *last = prev;
 }
 
-__global__ void __launch_bounds__(kThreads) ffdl_kernel(AllocArgs a, unsigned char* scratch, size_t slabBytes,
-                                                         int K4cap, int SW, int Jp) {
+// Per-round records the DP kernel leaves for the backtrack kernel.
+struct FfdlMeta {
+  int32_t J;     // rows of the DP (jobs kept after the trim)
+  int32_t st;    // VODA_ST_OK, or the panic raised before / by the DP
+  int32_t elem;  // bytes per SOL entry (1 or 2)
+  int32_t K;
+};
+
+struct FfdlScratch {
+  FfdlMeta* meta;      // [count]
+  int32_t* perm;       // [count][Jcap] sorted position -> job index within the round
+  unsigned char* sol;  // [count][Jcap][solStride]
+  size_t slabBytes;    // Jcap * solStrideMax
+  int Jcap;
+};
+
+// Kernel A: sort + DP rows.  One CTA per round at a time; SOL / perm / meta go to the round's
+// own slot of the scratch so that the CTA can move on to its next round immediately.
+__global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS) ffdl_dp_kernel(AllocArgs a, int r0, int count, FfdlScratch sc,
+                                                            int K4cap, int SW, int Jp) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FfdlSmem sm;
   {
@@ -229,94 +267,131 @@ __global__ void __launch_bounds__(kThreads) ffdl_kernel(AllocArgs a, unsigned ch
     sm.misc = reinterpret_cast<int*>(p);
   }
   const int tid = threadIdx.x;
-  unsigned char* slab = scratch + (size_t)blockIdx.x * slabBytes;
 
-  for (int r = blockIdx.x; r < a.rounds; r += gridDim.x) {
+  for (int rr = blockIdx.x; rr < count; rr += gridDim.x) {
+    const int r = r0 + rr;
     const int o = a.job_off[r] - a.job_base;
     const int n = a.job_off[r + 1] - a.job_off[r];
     const int K = a.total_gpu[r];
+    FfdlMeta meta{0, VODA_ST_OK, 1, K};
     if (n == 0) {  // :33-37 returns the empty result before anything else
-      if (tid == 0) a.out_status[r] = VODA_ST_OK;
+      if (tid == 0) sc.meta[rr] = meta;
       continue;
     }
     if (n > a.max_jobs || K > a.max_total) {
-      for (int i = tid; i < n; i += kThreads) a.out_gpus[o + i] = 0;
-      if (tid == 0) a.out_status[r] = VODA_ST_BOUND;
+      meta.st = VODA_ST_BOUND;
+      if (tid == 0) sc.meta[rr] = meta;
       continue;
     }
-    for (int i = tid; i < n; i += kThreads) a.out_gpus[o + i] = 0;  // :38-40
-    int st = VODA_ST_OK;
     if (K < 0) {
-      st = VODA_ST_RUNTIME_PANIC;  // make(ReadyJobs, 1, K+1) with cap < len (:54)
-    } else {
-      // 1. stable sort by SubmitTime
-      const int P2 = next_pow2(n);
-      for (int i = tid; i < n; i += kThreads) {
-        sm.khi[i] = a.submit_sec ? a.submit_sec[o + i] : 0;
-        sm.klo[i] = a.submit_nsec ? a.submit_nsec[o + i] : 0;
-      }
-      __syncthreads();
-      block_argsort(sm.khi, sm.klo, sm.perm, n, P2);
-      // 2. trim
-      const int J = min(n, K);
-      int lmax = 0;
-      for (int j = tid; j < J; j += kThreads) {
-        int mx = a.max_proc[o + sm.perm[j]];
-        sm.smax[j] = mx;
-        lmax = max(lmax, mx);
-      }
-      if (tid == 0) sm.misc[0] = 0;
-      __syncthreads();
-      for (int d = 16; d > 0; d >>= 1) lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, d));
-      if ((tid & 31) == 0) atomicMax(&sm.misc[0], lmax);
-      __syncthreads();
-      const int gmaxRound = min(sm.misc[0], K);
-      // 3-4. DP rows
-      const int KT = (K + kCells - 1) / kCells;
-      const float4* last = nullptr;
-      if (gmaxRound <= 255) {
-        const size_t solStride = (size_t)K4cap * 4;
-        ffdl_rows<uint8_t>(a, sm, o, J, K, KT, SW, solStride, slab, &last);
-        const float PJK = reinterpret_cast<const float*>(last)[K + 3];
-        if (PJK <= 0.0f) {
-          st = VODA_ST_INFEASIBLE;
-        } else if (tid == 0) {
-          int k = K;
-          for (int j = J; j > 0; j--) {
-            int g = k > 0 ? slab[(size_t)(j - 1) * solStride + (size_t)(k - 1)] : 0;  // SOL[j][0] == 0
-            a.out_gpus[o + sm.perm[j - 1]] = g;
-            k -= g;
-          }
-        }
-      } else {
-        const size_t solStride = (size_t)K4cap * 8;
-        ffdl_rows<uint16_t>(a, sm, o, J, K, KT, SW, solStride, slab, &last);
-        const float PJK = reinterpret_cast<const float*>(last)[K + 3];
-        if (PJK <= 0.0f) {
-          st = VODA_ST_INFEASIBLE;
-        } else if (tid == 0) {
-          int k = K;
-          for (int j = J; j > 0; j--) {
-            int g = k > 0 ? reinterpret_cast<const uint16_t*>(slab + (size_t)(j - 1) * solStride)[k - 1] : 0;
-            a.out_gpus[o + sm.perm[j - 1]] = g;
-            k -= g;
-          }
-        }
-      }
+      meta.st = VODA_ST_RUNTIME_PANIC;  // make(ReadyJobs, 1, K+1) with cap < len (:54)
+      if (tid == 0) sc.meta[rr] = meta;
+      continue;
     }
-    __syncthreads();  // out_gpus of this round written by thread 0 / zeroing threads
-    // 5. deferred validateResult: a panic it raises replaces the one in flight
-    int v = block_validate(a, o, n, K, a.out_gpus + o, nullptr, sm.red);
-    if (tid == 0) a.out_status[r] = v ? v : st;
+    __syncthreads();  // the previous round's shared state is dead
+    // 1. stable sort by SubmitTime
+    for (int i = tid; i < n; i += kThreads) {
+      sm.khi[i] = a.submit_sec ? a.submit_sec[o + i] : 0;
+      sm.klo[i] = a.submit_nsec ? a.submit_nsec[o + i] : 0;
+    }
+    __syncthreads();
+    block_argsort(sm.khi, sm.klo, sm.perm, n, next_pow2(n));
+    // 2. trim
+    const int J = min(n, K);
+    int lmax = 0;
+    int32_t* gperm = sc.perm + (size_t)rr * sc.Jcap;
+    for (int j = tid; j < J; j += kThreads) {
+      const int pj = sm.perm[j];
+      gperm[j] = pj;
+      const int mx = a.max_proc[o + pj];
+      sm.smax[j] = mx;
+      lmax = max(lmax, mx);
+    }
+    if (tid == 0) sm.misc[0] = 0;
+    __syncthreads();
+    for (int d = 16; d > 0; d >>= 1) lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, d));
+    if ((tid & 31) == 0) atomicMax(&sm.misc[0], lmax);
+    __syncthreads();
+    const int gmaxRound = min(sm.misc[0], K);
+    // 3-4. DP rows
+    const int KT = (K + kCells - 1) / kCells;
+    unsigned char* slab = sc.sol + (size_t)rr * sc.slabBytes;
+    const float4* last = nullptr;
+    if (gmaxRound <= 255) {
+      ffdl_rows<uint8_t>(a, sm, o, J, K, KT, SW, (size_t)K4cap * 4, slab, &last);
+      meta.elem = 1;
+    } else {
+      ffdl_rows<uint16_t>(a, sm, o, J, K, KT, SW, (size_t)K4cap * 8, slab, &last);
+      meta.elem = 2;
+    }
+    const float PJK = reinterpret_cast<const float*>(last)[K + 3];
+    meta.J = J;
+    if (PJK <= 0.0f) meta.st = VODA_ST_INFEASIBLE;  // :109-114 (NaN is not <= 0, as in Go)
+    if (tid == 0) sc.meta[rr] = meta;
+  }
+}
+
+// Kernel B: backtrack (:116-125) + deferred validateResult (:42).  One warp per round: the
+// chase through SOL is a chain of dependent loads, so thousands of rounds run it side by side.
+constexpr int kBtThreads = 128;
+__global__ void __launch_bounds__(kBtThreads) ffdl_backtrack_kernel(AllocArgs a, int r0, int count, FfdlScratch sc,
+                                                                    int K4cap) {
+  const int lane = threadIdx.x & 31;
+  const int rr = blockIdx.x * (kBtThreads / 32) + (threadIdx.x >> 5);
+  if (rr >= count) return;
+  const int r = r0 + rr;
+  const int o = a.job_off[r] - a.job_base;
+  const int n = a.job_off[r + 1] - a.job_off[r];
+  const FfdlMeta meta = sc.meta[rr];
+  if (n == 0) {
+    if (lane == 0) a.out_status[r] = VODA_ST_OK;
+    return;
+  }
+  for (int i = lane; i < n; i += 32) a.out_gpus[o + i] = 0;  // :38-40
+  if (meta.st == VODA_ST_BOUND) {
+    if (lane == 0) a.out_status[r] = VODA_ST_BOUND;
+    return;
+  }
+  __syncwarp();
+  if (meta.st == VODA_ST_OK && lane == 0) {
+    const unsigned char* slab = sc.sol + (size_t)rr * sc.slabBytes;
+    const int32_t* gperm = sc.perm + (size_t)rr * sc.Jcap;
+    const size_t stride = (size_t)K4cap * 4 * (size_t)meta.elem;
+    int k = meta.K;
+    for (int j = meta.J; j > 0; j--) {
+      int g = 0;  // SOL[j][0] == 0
+      if (k > 0) {
+        const unsigned char* row = slab + (size_t)(j - 1) * stride;
+        g = meta.elem == 1 ? (int)row[k - 1] : (int)reinterpret_cast<const uint16_t*>(row)[k - 1];
+      }
+      a.out_gpus[o + gperm[j - 1]] = g;
+      k -= g;
+    }
+  }
+  __syncwarp();
+  // validateResult (utils.go:18-42); a panic it raises replaces the one in flight
+  int worst = 99;
+  long long sum = 0;
+  for (int i = lane; i < n; i += 32) {
+    const int v = a.out_gpus[o + i];
+    int st = 99;
+    if (v < 0) st = VODA_ST_NEGATIVE;
+    else if (v > 0 && v < a.min_proc[o + i]) st = VODA_ST_LESS_THAN_MIN;
+    else if (v > a.max_proc[o + i]) st = VODA_ST_EXCEEDED_MAX;
+    worst = min(worst, st);
+    sum += v;
+  }
+  for (int d = 16; d > 0; d >>= 1) {
+    worst = min(worst, __shfl_xor_sync(0xffffffffu, worst, d));
+    sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  }
+  if (lane == 0) {
+    int v = worst != 99 ? worst : (sum > (long long)meta.K ? VODA_ST_EXCEEDED_TOTAL : VODA_ST_OK);
+    a.out_status[r] = v ? v : meta.st;
   }
 }
 
 }  // namespace
-
-int ffdl_grid(int sms, int rounds) {
-  int g = sms * 8;  // resident CTAs per SM (64 threads each)
-  return rounds < g ? (rounds > 0 ? rounds : 1) : g;
-}
 
 static void ffdl_shape(const AllocArgs& a, int* K4cap, int* SW, int* Jp, size_t* smem) {
   const int Kmax = a.max_total > 0 ? a.max_total : 1;
@@ -329,12 +404,18 @@ static void ffdl_shape(const AllocArgs& a, int* K4cap, int* SW, int* Jp, size_t*
           (sizeof(int64_t) + 3 * sizeof(int32_t)) * (size_t)(*Jp) + 2 * sizeof(long long) + 4 * sizeof(int);
 }
 
-size_t ffdl_scratch_bytes(const AllocArgs& a, int grid) {
+static size_t ffdl_jcap(const AllocArgs& a) {
+  const int j = a.max_jobs < a.max_total ? a.max_jobs : a.max_total;
+  return (size_t)(j > 0 ? j : 1);
+}
+
+// Scratch one round needs: its SOL slab (sized for 16-bit entries), perm row and meta record.
+size_t ffdl_scratch_per_round(const AllocArgs& a) {
   int K4cap, SW, Jp;
   size_t smem;
   ffdl_shape(a, &K4cap, &SW, &Jp, &smem);
-  const size_t Jcap = (size_t)(a.max_jobs < a.max_total ? a.max_jobs : a.max_total);
-  return (size_t)grid * (Jcap > 0 ? Jcap : 1) * (size_t)K4cap * 8;
+  const size_t Jcap = ffdl_jcap(a);
+  return Jcap * (size_t)K4cap * 8 + ((Jcap * 4 + 15) & ~(size_t)15) + sizeof(FfdlMeta);
 }
 
 size_t ffdl_smem_bytes(const AllocArgs& a) {
@@ -344,17 +425,36 @@ size_t ffdl_smem_bytes(const AllocArgs& a) {
   return smem;
 }
 
-cudaError_t launch_ffdl(const AllocArgs& a, int grid, void* scratch, size_t scratch_bytes,
-                        cudaStream_t stream) {
+// Rounds [r0, r0+count) of `a`: DP kernel then backtrack kernel.  `scratch` must hold
+// count * ffdl_scratch_per_round(a) bytes (256-byte aligned).
+cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* scratch, cudaStream_t stream) {
   int K4cap, SW, Jp;
   size_t smem;
   ffdl_shape(a, &K4cap, &SW, &Jp, &smem);
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(ffdl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(ffdl_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  const size_t slab = scratch_bytes / (size_t)grid;
-  ffdl_kernel<<<grid, kThreads, smem, stream>>>(a, static_cast<unsigned char*>(scratch), slab, K4cap, SW, Jp);
+  const size_t Jcap = ffdl_jcap(a);
+  const size_t permRow = (Jcap * 4 + 15) & ~(size_t)15;
+  FfdlScratch sc;
+  unsigned char* base = static_cast<unsigned char*>(scratch);
+  sc.slabBytes = Jcap * (size_t)K4cap * 8;
+  sc.Jcap = (int)(permRow / 4);
+  sc.sol = base;
+  sc.perm = reinterpret_cast<int32_t*>(base + (size_t)count * sc.slabBytes);
+  sc.meta = reinterpret_cast<FfdlMeta*>(base + (size_t)count * (sc.slabBytes + permRow));
+  int perSm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, ffdl_dp_kernel, kThreads, smem);
+  if (e != cudaSuccess) return e;
+  if (perSm < 1) perSm = 1;
+  int grid = sms * perSm;
+  if (count < grid) grid = count;
+  ffdl_dp_kernel<<<grid, kThreads, smem, stream>>>(a, r0, count, sc, K4cap, SW, Jp);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  const int perBlock = kBtThreads / 32;
+  ffdl_backtrack_kernel<<<(count + perBlock - 1) / perBlock, kBtThreads, 0, stream>>>(a, r0, count, sc, K4cap);
   return cudaGetLastError();
 }
 

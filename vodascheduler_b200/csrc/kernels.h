@@ -8,11 +8,10 @@
 namespace voda {
 
 // FfDLOptimizer (ffdl.cu)
-int ffdl_grid(int sms, int rounds);
-size_t ffdl_scratch_bytes(const AllocArgs& a, int grid);
+size_t ffdl_scratch_per_round(const AllocArgs& a);
 size_t ffdl_smem_bytes(const AllocArgs& a);
-cudaError_t launch_ffdl(const AllocArgs& a, int grid, void* scratch, size_t scratch_bytes,
-                        cudaStream_t stream);
+// rounds [r0, r0+count): DP kernel + backtrack kernel (2 launches)
+cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* scratch, cudaStream_t stream);
 
 // FIFO / SRJF / ElasticFIFO / ElasticSRJF (fill.cu)
 size_t fill_smem_bytes(const AllocArgs& a);

@@ -17,10 +17,10 @@
 // (no torch, no std::string, no staging buffers: inputs and outputs are the caller's device
 // pointers).
 //
-// Limits and sharing.  The array is 32 MiB.  One CTA needs a slab of
-// min(max_jobs, max_total_gpu) * ceil(max_total_gpu / 4) * 8 bytes; the launch uses as many
-// CTAs as fit (fewer CTAs than voda_allocate_dev would use, so it is slower on big batches),
-// and a batch whose single slab does not fit is rejected with VODA_E_TOO_LARGE.  All calls on
+// Limits and sharing.  The array is 32 MiB.  One round needs a slab of about
+// min(max_jobs, max_total_gpu) * ceil(max_total_gpu / 4) * 8 bytes; the batch is walked in
+// passes of as many rounds as fit (so it is slower than voda_allocate_dev on big batches),
+// and a batch whose single round does not fit is rejected with VODA_E_TOO_LARGE.  All calls on
 // a GPU share the one array and it keeps whatever the previous call left in it.  Nothing has
 // to start at zero: each DP row rewrites its whole SOL row before the backtrack reads any cell
 // of it, so no clearing is done.  Two calls that overlap on the GPU (different streams, or
@@ -112,17 +112,19 @@ extern "C" int voda_ffdl_allocate_static(void* stream, const voda_alloc_batch* b
 
   if (ffdl_smem_bytes(a) > 200 * 1024)
     return report(errbuf, errbuf_len, VODA_E_UNSUPPORTED, "total_gpu / jobs too large for one CTA's shared memory");
-  const size_t slab = ffdl_scratch_bytes(a, 1);  // bytes one CTA needs
-  if (slab > VODA_STATIC_SCRATCH_BYTES) {
+  const size_t per = (ffdl_scratch_per_round(a) + 255) & ~(size_t)255;  // bytes one round needs
+  if (per > VODA_STATIC_SCRATCH_BYTES) {
     char detail[160];
-    std::snprintf(detail, sizeof detail, "one round needs %zu bytes of SOL scratch, the fixed array holds %u", slab,
+    std::snprintf(detail, sizeof detail, "one round needs %zu bytes of SOL scratch, the fixed array holds %u", per,
                   (unsigned)VODA_STATIC_SCRATCH_BYTES);
     return report(errbuf, errbuf_len, VODA_E_TOO_LARGE, "batch shape exceeds the static scratch", detail);
   }
-  int grid = ffdl_grid(sms, a.rounds);
-  const int fit = (int)(VODA_STATIC_SCRATCH_BYTES / slab);
-  if (grid > fit) grid = fit;
-  e = launch_ffdl(a, grid, scratch, (size_t)grid * slab, static_cast<cudaStream_t>(stream));
-  if (e != cudaSuccess) return report(errbuf, errbuf_len, VODA_E_CUDA, "FfDL kernel launch", cudaGetErrorString(e));
+  // as many rounds per pass as the array holds; each pass is a DP launch + a backtrack launch
+  const int fit = (int)(VODA_STATIC_SCRATCH_BYTES / per);
+  for (int r0 = 0; r0 < a.rounds; r0 += fit) {
+    const int count = a.rounds - r0 < fit ? a.rounds - r0 : fit;
+    e = launch_ffdl(a, r0, count, sms, scratch, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return report(errbuf, errbuf_len, VODA_E_CUDA, "FfDL kernel launch", cudaGetErrorString(e));
+  }
   return VODA_OK;
 }
