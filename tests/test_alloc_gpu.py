@@ -103,8 +103,10 @@ def test_ffdl_wide_max_and_table_edge(ctx, oracle):
 
 @pytest.mark.parametrize("algo", ALGOS)
 def test_chunked_pipeline_equals_single(ctx, oracle, algo):
-    """A batch large enough to be cut into several pipeline chunks gives the same answer."""
-    b = synth.jobs_batch(algo, rounds=3000, jobs_per_round=32, total_gpu=64, ragged=True)
+    """A batch large enough to be cut into several pipeline chunks (>= 16 MiB and >= 12 rounds
+    per SM each) gives the same answer as the oracle computes in one piece."""
+    rounds = 9000 if algo in ("AFS-L", "ElasticTiresias", "FfDLOptimizer") else 30000
+    b = synth.jobs_batch(algo, rounds=rounds, jobs_per_round=48, total_gpu=40, ragged=True)
     _same(ctx, oracle, b)
 
 

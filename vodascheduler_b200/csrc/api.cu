@@ -341,13 +341,14 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
   if (f & F_MAX) per_job += 4;
   if (f & F_REM) per_job += 4;
   per_job += 4 * W;
-  // chunking: ~8 MiB of staged bytes per chunk, at least 4 chunks when the batch allows
+  // chunking: a chunk must hold enough rounds to occupy every SM (one CTA per round, about a
+  // dozen resident CTAs per SM) and at least ~16 MiB so the copies run at PCIe speed; several
+  // chunks per batch let the H2D copy of one overlap the kernels of the previous one
   const size_t total_bytes = per_job * (size_t)off[R] + 12 * (size_t)R;
-  size_t target = 8u << 20;
-  int chunks = (int)std::min<size_t>((size_t)R, std::max<size_t>(1, (total_bytes + target - 1) / target));
-  if (chunks < 4 && R >= 4 && total_bytes > (1u << 20)) chunks = 4;
-  const int rounds_per = (R + chunks - 1) / chunks;
-
+  const size_t bytes_per_round = std::max<size_t>(1, total_bytes / (size_t)R);
+  size_t rounds_per_sz = std::max<size_t>((size_t)ctx->sms * 12, ((size_t)16 << 20) / bytes_per_round + 1);
+  if (rounds_per_sz > (size_t)R) rounds_per_sz = (size_t)R;
+  const int rounds_per = (int)rounds_per_sz;
   for (int c = 0, r0 = 0; r0 < R; c++, r0 += rounds_per) {
     const int r1 = std::min(R, r0 + rounds_per);
     const int slot = c & 1;
