@@ -125,41 +125,56 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
   }
   __syncwarp();
 
-  uint32_t rowCov[4] = {0, 0, 0, 0};
+  // Covers.  Columns: a uniform 128-bit mask.  Rows: each lane keeps the 4 cover bits of the rows
+  // it owns (`ownCov`); the uniform row mask is only rebuilt for step 6.
+  uint32_t ownCov = 0;
   uint32_t colCov[4] = {starred[0], starred[1], starred[2], starred[3]};  // step 3
   bool ucolValid[4];
 #pragma unroll
   for (int t = 0; t < 4; t++) ucolValid[t] = lane + 32 * t < n;
 
-  while (nstar < n) {
-    // ---- step 4: first uncovered zero in row-major order
-    const uint32_t own = own_rows(rowCov, lane);
-    int myq = -1, mycol = 0;
+  // first[q]: the first uncovered zero of owned row q (kNone if it has none).  Inside one
+  // step-4 phase columns only get UNcovered and rows only get covered, so after a column sc is
+  // uncovered the new value is min(first[q], sc) for the rows that have a zero there: the
+  // search "first uncovered zero in row-major order" never rescans the masks.
+  constexpr int kNone = 255;
+  int first[4];
+  auto recompute_first = [&]() {
 #pragma unroll
-    for (int q = 3; q >= 0; q--) {
-      if (!((own >> q) & 1u)) {
-        int col = -1;
+    for (int q = 0; q < 4; q++) {
+      first[q] = kNone;
 #pragma unroll
-        for (int t = 3; t >= 0; t--) {
-          const uint32_t cand = Z[q][t] & ~colCov[t];
-          if (cand) col = 32 * t + __ffs(cand) - 1;
-        }
-        if (col >= 0) {
-          myq = q;
-          mycol = col;
-        }
+      for (int t = 3; t >= 0; t--) {
+        const uint32_t cand = Z[q][t] & ~colCov[t];
+        if (cand) first[q] = 32 * t + __ffs(cand) - 1;
       }
     }
-    const unsigned b = __ballot_sync(full, myq >= 0);
+  };
+  recompute_first();
+
+  while (nstar < n) {
+    // ---- step 4: first uncovered zero in row-major order
+    int key = 0x7fffffff;
+#pragma unroll
+    for (int q = 3; q >= 0; q--)
+      if (!((ownCov >> q) & 1u) && first[q] != kNone) key = (q << 8) | first[q];
+    const unsigned b = __ballot_sync(full, key != 0x7fffffff);
     if (b) {
       const int ls = __ffs(b) - 1;
-      const int packed = __shfl_sync(full, (myq << 8) | mycol, ls);
+      const int packed = __shfl_sync(full, key, ls);
       const int row = 4 * ls + (packed >> 8), col = packed & 255;
       const int sc = sm.starCol[row];
       if (sc >= 0) {  // prime it, cover its row, uncover the star's column
         if (lane == 0) sm.primeCol[row] = (short)col;
-        mask_set(rowCov, row);
+        if (lane == ls) ownCov |= 1u << (packed >> 8);
         mask_clear(colCov, sc);
+        const int tw = sc >> 5;
+        const uint32_t bit = 1u << (sc & 31);
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const uint32_t wsel = tw == 0 ? Z[q][0] : tw == 1 ? Z[q][1] : tw == 2 ? Z[q][2] : Z[q][3];
+          if (wsel & bit) first[q] = min(first[q], sc);
+        }
         continue;
       }
       // ---- step 5: augment along the alternating path that starts at the prime (row, col)
@@ -180,13 +195,20 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
       __syncwarp();
       mask_set(starred, last);  // the path ends in the one column that gains a star
       nstar++;
+      ownCov = 0;  // clear covers, erase primes (stale primes are never read)
 #pragma unroll
-      for (int t = 0; t < 4; t++) {
-        rowCov[t] = 0;           // clear covers, erase primes (stale primes are never read)
-        colCov[t] = starred[t];  // step 3
-      }
+      for (int t = 0; t < 4; t++) colCov[t] = starred[t];  // step 3
+      recompute_first();
       continue;
     }
+    // rebuild the uniform row-cover mask from the per-lane bits (rows 4*lane .. 4*lane+3)
+    uint32_t rowCov[4];
+    {
+      const uint32_t nib = ownCov << (4 * (lane & 7));
+#pragma unroll
+      for (int w = 0; w < 4; w++) rowCov[w] = __reduce_or_sync(full, (lane >> 3) == w ? nib : 0u);
+    }
+    const uint32_t own = ownCov;
     // ---- step 6: m = smallest uncovered value; covered rows += m, uncovered columns -= m
     bool ucol[4];
 #pragma unroll
@@ -235,6 +257,7 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
         }
       }
     }
+    recompute_first();  // the masks changed; covers did not
   }
   __syncwarp();
 }
