@@ -422,7 +422,7 @@ int voda_munkres_max_dev(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t*
     CU(cudaMemsetAsync(d_status, 0, 4 * (size_t)batch, ctx->stream));
     return VODA_OK;
   }
-  int rc = ensure(ctx, ctx->scratch, munkres_scratch_bytes(batch), ctx->stream);
+  int rc = ensure(ctx, ctx->scratch, munkres_scratch_bytes(n, batch, ctx->sms), ctx->stream);
   if (rc) return rc;
   int launched = 0;
   CU(launch_munkres(n, batch, d_A, d_out, d_status, ctx->scratch.p, ctx->sms, ctx->stream, &launched));
@@ -442,15 +442,15 @@ int voda_munkres_max(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t* A, 
   }
   CU(cudaSetDevice(ctx->device));
   const size_t per = (size_t)n * n * 8;
-  // chunks big enough to occupy every SM (16 matrices per SM), at least ~8 MiB
-  size_t per_chunk = std::max<size_t>((size_t)ctx->sms * 16, (8u << 20) / per + 1);
+  // chunks big enough to occupy every SM (32 one-warp CTAs per SM), at least ~8 MiB
+  size_t per_chunk = std::max<size_t>((size_t)ctx->sms * 32, (8u << 20) / per + 1);
   if (per_chunk > (size_t)batch) per_chunk = (size_t)batch;
   for (size_t c = 0, b0 = 0; b0 < (size_t)batch; c++, b0 += per_chunk) {
     const size_t nb = std::min(per_chunk, (size_t)batch - b0);
     const int slot = (int)(c & 1);
     cudaStream_t s = ctx->pipe[slot];
     const size_t o_A = 0, o_out = align256(per * nb), o_st = o_out + align256(4 * nb * n),
-                 o_need = o_st + align256(4 * nb), total = o_need + munkres_scratch_bytes((int)nb);
+                 o_need = o_st + align256(4 * nb), total = o_need + munkres_scratch_bytes(n, (int)nb, ctx->sms);
     int rc = ensure(ctx, ctx->stage[slot], total, s);
     if (rc) return rc;
     char* base = (char*)ctx->stage[slot].p;

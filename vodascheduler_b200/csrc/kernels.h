@@ -26,7 +26,7 @@ size_t afsl_smem_bytes(const AllocArgs& a);
 cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream);
 
 // batched ComputeMunkresMax (munkres.cu)
-size_t munkres_scratch_bytes(int batch);
+size_t munkres_scratch_bytes(int n, int batch, int sms);
 cudaError_t launch_munkres(int n, int batch, const int64_t* A, int32_t* out, int32_t* status, void* scratch,
                            int sms, cudaStream_t stream, int* launched);
 

@@ -2,12 +2,15 @@
 // github.com/heyfey/munkres) : one warp-sized CTA per n x n int64 score matrix.
 //
 // The matrix is read once from HBM (coalesced 256-byte row segments), turned into
-// C[i][j] = rowmax_i - A[i][j] and parked in shared memory in the NARROWEST cell type that
-// holds every C value, because shared memory per matrix sets how many matrices an SM works on
-// at once (16 KB as uint8 -> 12 per SM; 128 KB as int64 -> 1 per SM).  The type is found by
-// trying: the uint8 kernel runs over the whole batch and marks the matrices whose range does
-// not fit; the uint16 / int32 / int64 kernels then pick up only what was marked (each is an
-// almost-empty launch when nothing was).  The solve itself is munkres.cuh.
+// C[i][j] = rowmax_i - A[i][j] and parked in the NARROWEST cell type that holds every C value.
+// C is only read again by step 6 (a handful of times per matrix), so it lives in a per-CTA
+// slab of global scratch that stays L2-resident (16 KB per matrix as uint8), NOT in shared
+// memory: the solve is a chain of dependent warp steps, throughput comes from how many
+// matrices an SM works on at once, and with ~1.3 KB of shared memory per matrix that is the
+// hardware limit of 32 one-warp CTAs per SM.  The cell type is found by trying: the uint8
+// kernel runs over the whole batch and marks the matrices whose range does not fit; the
+// uint16 / int32 / int64 kernels then pick up only what was marked (each is an almost-empty
+// launch when nothing was).  The solve itself is munkres.cuh.
 #include "kernels.h"
 #include "munkres.cuh"
 
@@ -32,16 +35,19 @@ __device__ __forceinline__ long long warp_max_ll(long long v) {
 template <typename CellT>
 __global__ void __launch_bounds__(32) munkres_kernel(int n, int batch, const int64_t* __restrict__ A,
                                                      int32_t* __restrict__ out, int32_t* __restrict__ status,
-                                                     unsigned char* __restrict__ need, int level) {
+                                                     unsigned char* __restrict__ need, int level,
+                                                     unsigned char* __restrict__ slabs, size_t slabBytes) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   using Pot = typename MunkresTypes<CellT>::Pot;
-  CellT* C = reinterpret_cast<CellT*>(smem_raw);
-  size_t off = ((size_t)n * n * sizeof(CellT) + 15) & ~(size_t)15;
+  CellT* C = reinterpret_cast<CellT*>(slabs + (size_t)blockIdx.x * slabBytes);
+  size_t off = 0;
   MunkresSmem sm;
   sm.ra = smem_raw + off; off += 128 * sizeof(Pot);
   sm.starCol = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
   sm.starRow = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
-  sm.primeCol = reinterpret_cast<short*>(smem_raw + off);
+  sm.primeCol = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
+  sm.zt = reinterpret_cast<uint32_t*>(smem_raw + off); off += 128 * 4 * sizeof(uint32_t);
+  sm.ccs = reinterpret_cast<uint32_t*>(smem_raw + off);
   const int lane = threadIdx.x;
   const unsigned full = 0xffffffffu;
   const long long NEG = (long long)0x8000000000000000ULL;
@@ -55,6 +61,7 @@ __global__ void __launch_bounds__(32) munkres_kernel(int n, int batch, const int
 #pragma unroll
       for (int t = 0; t < 4; t++) Z[q][t] = 0;
     bool overflow = false;
+    for (int x = lane; x < 128 * 4; x += 32) sm.zt[x] = 0;
     __syncwarp();
     for (int l = 0; l < 32 && 4 * l < n; l++) {
       // 4 rows x 4 column blocks in flight
@@ -75,7 +82,20 @@ __global__ void __launch_bounds__(32) munkres_kernel(int n, int batch, const int
         long long mx = v[q][0];
 #pragma unroll
         for (int t = 1; t < 4; t++) mx = v[q][t] > mx ? v[q][t] : mx;
-        mx = warp_max_ll(mx);
+        {
+          // rows whose valid entries share one high word (the usual case: small scores) reduce
+          // on the low words with a single redux; others take the 64-bit shuffle tree
+          const int hi0 = __shfl_sync(full, (int)(v[q][0] >> 32), 0);  // column 0 is always valid
+          bool same = true;
+#pragma unroll
+          for (int t = 0; t < 4; t++) same = same && (lane + 32 * t >= n || (int)(v[q][t] >> 32) == hi0);
+          if (__all_sync(full, same)) {
+            const unsigned lo = __reduce_max_sync(full, (unsigned)(unsigned long long)mx);
+            mx = (long long)(((unsigned long long)(unsigned)hi0 << 32) | lo);
+          } else {
+            mx = warp_max_ll(mx);
+          }
+        }
 #pragma unroll
         for (int t = 0; t < 4; t++) {
           const int col = lane + 32 * t;
@@ -87,6 +107,7 @@ __global__ void __launch_bounds__(32) munkres_kernel(int n, int batch, const int
           if (valid) C[(size_t)i * n + col] = (CellT)c;
           const unsigned bz = __ballot_sync(full, valid && c == 0);
           if (lane == l) Z[q][t] = bz;
+          if (valid && c == 0) sm.zt[col * 4 + (i >> 5)] |= 1u << (i & 31);  // this lane owns column col
         }
       }
     }
@@ -108,45 +129,47 @@ __global__ void __launch_bounds__(32) munkres_kernel(int n, int batch, const int
 }
 
 template <typename CellT>
-size_t munkres_smem(int n) {
+size_t munkres_smem() {
   using Pot = typename MunkresTypes<CellT>::Pot;
-  return (((size_t)n * n * sizeof(CellT) + 15) & ~(size_t)15) + 128 * sizeof(Pot) + 3 * 128 * sizeof(short) + 16;
+  return 128 * sizeof(Pot) + 3 * 128 * sizeof(short) + 128 * 4 * sizeof(uint32_t) + 4 * sizeof(uint32_t) + 16;
 }
+
+constexpr int kCtasPerSm = 32;  // one-warp CTAs: the hardware limit of resident CTAs per SM
+
+// every level shares one slab region: narrower cells -> more resident matrices
+size_t slab_region_bytes(int n, int sms) { return (size_t)sms * kCtasPerSm * (((size_t)n * n + 255) & ~(size_t)255); }
 
 template <typename CellT>
 cudaError_t launch_level(int n, int batch, const int64_t* A, int32_t* out, int32_t* status, unsigned char* need,
-                         int level, int sms, cudaStream_t stream) {
-  const size_t smem = munkres_smem<CellT>(n);
+                         int level, int sms, unsigned char* slabs, cudaStream_t stream) {
+  const size_t smem = munkres_smem<CellT>();
   auto kern = munkres_kernel<CellT>;
-  if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-  }
-  int perSm = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, 32, smem);
-  if (e != cudaSuccess) return e;
-  if (perSm < 1) perSm = 1;
-  int grid = sms * perSm;
+  const size_t slabBytes = (((size_t)n * n + 255) & ~(size_t)255) * sizeof(CellT);
+  int grid = (int)(slab_region_bytes(n, sms) / slabBytes);  // sms * 32 / sizeof(CellT)
+  if (grid < 1) grid = 1;
   if (batch < grid) grid = batch;
-  kern<<<grid, 32, smem, stream>>>(n, batch, A, out, status, need, level);
+  kern<<<grid, 32, smem, stream>>>(n, batch, A, out, status, need, level, slabs, slabBytes);
   return cudaGetLastError();
 }
 
 }  // namespace
 
-size_t munkres_scratch_bytes(int batch) { return ((size_t)batch + 255) & ~(size_t)255; }
+size_t munkres_scratch_bytes(int n, int batch, int sms) {
+  return (((size_t)batch + 255) & ~(size_t)255) + slab_region_bytes(n, sms);
+}
 
 // Enqueues memset + up to four kernels; returns the number of kernels launched in *launched.
 cudaError_t launch_munkres(int n, int batch, const int64_t* A, int32_t* out, int32_t* status, void* scratch,
                            int sms, cudaStream_t stream, int* launched) {
   unsigned char* need = static_cast<unsigned char*>(scratch);
+  unsigned char* slabs = need + (((size_t)batch + 255) & ~(size_t)255);
   cudaError_t e = cudaMemsetAsync(need, 0, (size_t)batch, stream);
   if (e != cudaSuccess) return e;
   *launched = 0;
-  if ((e = launch_level<uint8_t>(n, batch, A, out, status, need, 0, sms, stream)) != cudaSuccess) return e;
-  if ((e = launch_level<uint16_t>(n, batch, A, out, status, need, 1, sms, stream)) != cudaSuccess) return e;
-  if ((e = launch_level<int32_t>(n, batch, A, out, status, need, 2, sms, stream)) != cudaSuccess) return e;
-  if ((e = launch_level<int64_t>(n, batch, A, out, status, need, 3, sms, stream)) != cudaSuccess) return e;
+  if ((e = launch_level<uint8_t>(n, batch, A, out, status, need, 0, sms, slabs, stream)) != cudaSuccess) return e;
+  if ((e = launch_level<uint16_t>(n, batch, A, out, status, need, 1, sms, slabs, stream)) != cudaSuccess) return e;
+  if ((e = launch_level<int32_t>(n, batch, A, out, status, need, 2, sms, slabs, stream)) != cudaSuccess) return e;
+  if ((e = launch_level<int64_t>(n, batch, A, out, status, need, 3, sms, slabs, stream)) != cudaSuccess) return e;
   *launched = 4;
   return cudaSuccess;
 }

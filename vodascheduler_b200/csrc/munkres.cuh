@@ -15,8 +15,9 @@
 //     "first uncovered zero in row-major order" (step 4, ~n^2/16 times per matrix) is one
 //     ballot + two find-first-set instead of an n^2 scan; step 6 patches the masks (covered
 //     rows lose their zeros in covered columns; uncovered x uncovered cells equal to m gain one);
-//   * stars / primes are starCol[row], starRow[col], primeCol[row] in shared memory; row and
-//     column covers are uniform 128-bit masks in registers.
+//   * stars / primes are starCol[row], starRow[col], primeCol[row] in shared memory, and so
+//     are the column covers and a column-major copy of the zero masks (which rows have a zero
+//     in column j), so that a step-4 iteration is ~40 instructions.
 #pragma once
 
 #include "common.cuh"
@@ -41,6 +42,9 @@ struct MunkresSmem {
   short* starRow;   // [128] row of the star in column j, -1 if none
   short* primeCol;  // [128] column of the prime in row i (valid for rows covered in this phase)
   void* ra;         // [128] row potentials (Pot)
+  uint32_t* zt;     // [128][4] column-major zero masks: bit i of zt[j] = (value(i, j) == 0);
+                    //          the caller fills it together with the row-major masks Z
+  uint32_t* ccs;    // [4] column covers
 };
 
 __device__ __forceinline__ void mask_set(uint32_t (&m)[4], int idx) {
@@ -125,56 +129,62 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
   }
   __syncwarp();
 
-  // Covers.  Columns: a uniform 128-bit mask.  Rows: each lane keeps the 4 cover bits of the rows
-  // it owns (`ownCov`); the uniform row mask is only rebuilt for step 6.
-  uint32_t ownCov = 0;
+  // Covers.  Columns: 128 bits in shared memory (sm.ccs), copied to registers when a whole
+  // mask is needed.  Rows: each lane keeps the state of the 4 rows it owns.
+  //
+  // k[q] = (q << 8) | first uncovered zero column of owned row q, or kBig when the row is
+  // covered or has none.  Inside one step-4 phase columns only get UNcovered and rows only get
+  // covered, so uncovering column sc turns k[q] into min(k[q], (q << 8) | sc) for the live rows
+  // that have a zero there — read from the column-major zero masks sm.zt — and the search
+  // "first uncovered zero in row-major order" never rescans anything: it is the minimum key
+  // of the lowest lane that has one.
+  constexpr int kBig = 0x7fffffff;
   uint32_t colCov[4] = {starred[0], starred[1], starred[2], starred[3]};  // step 3
   bool ucolValid[4];
 #pragma unroll
   for (int t = 0; t < 4; t++) ucolValid[t] = lane + 32 * t < n;
-
-  // first[q]: the first uncovered zero of owned row q (kNone if it has none).  Inside one
-  // step-4 phase columns only get UNcovered and rows only get covered, so after a column sc is
-  // uncovered the new value is min(first[q], sc) for the rows that have a zero there: the
-  // search "first uncovered zero in row-major order" never rescans the masks.
-  constexpr int kNone = 255;
-  int first[4];
-  auto recompute_first = [&]() {
+  int k[4];
+  uint32_t live = 0xFu;  // owned rows not covered
+  auto reset_phase = [&]() {  // covers = {starred columns}, no row; keys from the zero masks
+    if (lane < 4) sm.ccs[lane] = lane == 0 ? colCov[0] : lane == 1 ? colCov[1] : lane == 2 ? colCov[2] : colCov[3];
+    live = 0xFu;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
-      first[q] = kNone;
+      k[q] = kBig;
 #pragma unroll
       for (int t = 3; t >= 0; t--) {
         const uint32_t cand = Z[q][t] & ~colCov[t];
-        if (cand) first[q] = 32 * t + __ffs(cand) - 1;
+        if (cand) k[q] = (q << 8) | (32 * t + __ffs(cand) - 1);
       }
     }
+    __syncwarp();
   };
-  recompute_first();
+  reset_phase();
+  const int ztWord = lane >> 3, ztShift = 4 * (lane & 7);
 
   while (nstar < n) {
     // ---- step 4: first uncovered zero in row-major order
-    int key = 0x7fffffff;
-#pragma unroll
-    for (int q = 3; q >= 0; q--)
-      if (!((ownCov >> q) & 1u) && first[q] != kNone) key = (q << 8) | first[q];
-    const unsigned b = __ballot_sync(full, key != 0x7fffffff);
+    const int key = min(min(k[0], k[1]), min(k[2], k[3]));
+    const unsigned b = __ballot_sync(full, key != kBig);
     if (b) {
       const int ls = __ffs(b) - 1;
       const int packed = __shfl_sync(full, key, ls);
       const int row = 4 * ls + (packed >> 8), col = packed & 255;
       const int sc = sm.starCol[row];
       if (sc >= 0) {  // prime it, cover its row, uncover the star's column
-        if (lane == 0) sm.primeCol[row] = (short)col;
-        if (lane == ls) ownCov |= 1u << (packed >> 8);
-        mask_clear(colCov, sc);
-        const int tw = sc >> 5;
-        const uint32_t bit = 1u << (sc & 31);
-#pragma unroll
-        for (int q = 0; q < 4; q++) {
-          const uint32_t wsel = tw == 0 ? Z[q][0] : tw == 1 ? Z[q][1] : tw == 2 ? Z[q][2] : Z[q][3];
-          if (wsel & bit) first[q] = min(first[q], sc);
+        if (lane == 0) {
+          sm.primeCol[row] = (short)col;
+          sm.ccs[sc >> 5] &= ~(1u << (sc & 31));
         }
+        if (lane == ls) {  // the chosen key is this lane's k[q] of the covered row
+          live &= ~(1u << (packed >> 8));
+#pragma unroll
+          for (int q = 0; q < 4; q++) k[q] = k[q] == packed ? kBig : k[q];
+        }
+        const uint32_t hits = (sm.zt[sc * 4 + ztWord] >> ztShift) & live;
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if ((hits >> q) & 1u) k[q] = min(k[q], (q << 8) | sc);
         continue;
       }
       // ---- step 5: augment along the alternating path that starts at the prime (row, col)
@@ -195,12 +205,16 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
       __syncwarp();
       mask_set(starred, last);  // the path ends in the one column that gains a star
       nstar++;
-      ownCov = 0;  // clear covers, erase primes (stale primes are never read)
 #pragma unroll
-      for (int t = 0; t < 4; t++) colCov[t] = starred[t];  // step 3
-      recompute_first();
+      for (int t = 0; t < 4; t++) colCov[t] = starred[t];  // step 3; covers cleared, primes stale
+      reset_phase();
       continue;
     }
+    // ---- step 6 needs whole masks: columns from shared memory, rows from the per-lane bits
+    __syncwarp();
+#pragma unroll
+    for (int t = 0; t < 4; t++) colCov[t] = sm.ccs[t];
+    const uint32_t ownCov = ~live & 0xFu;
     // rebuild the uniform row-cover mask from the per-lane bits (rows 4*lane .. 4*lane+3)
     uint32_t rowCov[4];
     {
@@ -232,12 +246,19 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
 #pragma unroll
     for (int t = 0; t < 4; t++)
       if (ucol[t]) cs[t] += mn;
-    // zeros of covered rows in covered columns become positive
+    // zeros of covered rows in covered columns become positive (row-major and column-major masks)
 #pragma unroll
     for (int q = 0; q < 4; q++)
       if ((own >> q) & 1u) {
 #pragma unroll
         for (int t = 0; t < 4; t++) Z[q][t] &= ~colCov[t];
+      }
+#pragma unroll
+    for (int t = 0; t < 4; t++)
+      if (ucolValid[t] && ((colCov[t] >> lane) & 1u)) {
+        uint32_t* z = sm.zt + (lane + 32 * t) * 4;
+#pragma unroll
+        for (int w = 0; w < 4; w++) z[w] &= ~rowCov[w];
       }
     __syncwarp();
     // uncovered x uncovered cells that were equal to m become zeros
@@ -254,10 +275,23 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
           const bool z = ucol[t] && ((Pot)row[lane + 32 * t] + rai - cs[t] == 0);
           const unsigned bz = __ballot_sync(full, z);
           if (lane == l) Z[q][t] |= bz;
+          if (z) sm.zt[(lane + 32 * t) * 4 + (i >> 5)] |= 1u << (i & 31);
         }
       }
     }
-    recompute_first();  // the masks changed; covers did not
+    __syncwarp();
+    // the masks changed; the covers did not: rebuild the keys of the live rows
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      k[q] = kBig;
+      if ((live >> q) & 1u) {
+#pragma unroll
+        for (int t = 3; t >= 0; t--) {
+          const uint32_t cand = Z[q][t] & ~colCov[t];
+          if (cand) k[q] = (q << 8) | (32 * t + __ffs(cand) - 1);
+        }
+      }
+    }
   }
   __syncwarp();
 }

@@ -59,7 +59,9 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp) {
     sm.rowmax = reinterpret_cast<int32_t*>(p); p += 4 * 128;
     sm.mk.starCol = reinterpret_cast<short*>(p); p += 2 * 128;
     sm.mk.starRow = reinterpret_cast<short*>(p); p += 2 * 128;
-    sm.mk.primeCol = reinterpret_cast<short*>(p);
+    sm.mk.primeCol = reinterpret_cast<short*>(p); p += 2 * 128;
+    sm.mk.zt = reinterpret_cast<uint32_t*>(p); p += 4 * 4 * 128;
+    sm.mk.ccs = reinterpret_cast<uint32_t*>(p);
   }
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned full = 0xffffffffu;
@@ -244,6 +246,8 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp) {
       for (int q = 0; q < 4; q++)
 #pragma unroll
         for (int t = 0; t < 4; t++) Z[q][t] = 0;
+      for (int x = lane; x < 128 * 4; x += 32) sm.mk.zt[x] = 0;
+      __syncwarp();
       for (int l = 0; l < 32 && 4 * l < n; l++) {
 #pragma unroll
         for (int q = 0; q < 4; q++) {
@@ -267,6 +271,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp) {
             if (ok) sm.M[i * n + col] = c;
             const unsigned bz = __ballot_sync(full, ok && c == 0);
             if (lane == l) Z[q][t] = bz;
+            if (ok && c == 0) sm.mk.zt[col * 4 + (i >> 5)] |= 1u << (i & 31);
           }
         }
       }
@@ -291,7 +296,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp) {
 
 size_t place_smem(int maxNodes, int Mp) {
   return 4 * (size_t)maxNodes * maxNodes + 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 8 * 128 +
-         4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 64;
+         4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 4 * 4 * 128 + 16 + 64;
 }
 
 }  // namespace
