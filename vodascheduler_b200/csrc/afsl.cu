@@ -12,15 +12,22 @@
 //     evaluate(short, long) = (S_l[r_l+1]-S_l[r_l]) / S_l[r_l+1]  >  (S_s[r_s+1]-S_s[r_s]) / S_s[r_s]
 // A tree reduction would change results, so the fold order is kept exactly:
 //   * one warp walks the live list 32 challengers at a time against the current champion; a
-//     ballot finds the FIRST challenger that replaces it, that one becomes the champion and
-//     only the lanes after it re-evaluate (speculative first-beat scan);
+//     ballot finds the FIRST challenger that replaces it, that lane broadcasts its whole state
+//     by shuffle and becomes the champion, and only the lanes after it re-evaluate
+//     (speculative first-beat scan);
 //   * the champion entering every position is cached; after the winner at position p gets its
 //     GPU the next fold restarts at p with the cached champion (positions before p never
 //     involve the winner, so their outcome cannot change);
-//   * the divisions are hoisted: len(x, w) = rem_x / S_x[w] is tabulated once per round for
-//     every (job, w) in shared memory (same float32 quotient the reference computes each
-//     time), and the two evaluate() ratios of a job are recomputed only when its count changes.
-// Removal at max keeps order (lazy deletion + periodic compaction of the live list).
+//   * the divisions are hoisted: len(x, w) = rem_x / S_x[w] (the float32 quotient the reference
+//     recomputes every step) is tabulated once per round for the HOT worker counts
+//     w = 1 .. CH in shared memory, column-major over the jobs in sorted order so that 32
+//     neighbouring challengers read 32 neighbouring banks; larger w (rare: the champion's count
+//     is small) divide on the fly from the table in HBM; the two evaluate() ratios of a job are
+//     recomputed only when its count changes.
+// The dependent chain (picks x fold steps) is the cost; throughput comes from rounds in flight,
+// so shared memory per round is kept small (28 bytes per job + CH * 4) to fit 4 CTAs per SM.
+// Jobs are relabelled by their sorted position; removal at max keeps order (lazy deletion +
+// periodic compaction of the live list).
 #include "common.cuh"
 #include "kernels.h"
 
@@ -28,39 +35,46 @@ namespace voda {
 namespace {
 
 constexpr int kThreads = 128;
+constexpr unsigned short kDead = 0xFFFF;
 
 struct AfslSmem {
-  int64_t* khi;
-  long long* red;   // [4]
-  int32_t* klo;
-  int* order;       // live list (job ids in SubmitTime order), dead entries = -1
-  int* champIn;     // champion entering each position of `order` ...
-  int* champInPos;  // ... and the position that champion sits at
+  // indexed by sorted position ("sr")
+  float* rem;
+  float* L;    // (S[r+1]-S[r]) / S[r+1]   "as the longer job"
+  float* Rr;   // (S[r+1]-S[r]) / S[r]     "as the shorter job"
   int32_t* r;
   int32_t* mx;
-  float* rem;
-  float* L;         // (S[r+1]-S[r]) / S[r+1]   "as the longer job"
-  float* Rr;        // (S[r+1]-S[r]) / S[r]     "as the shorter job"
-  float* lenT;      // [n * W] rem / S[w]  (w = 0: +Inf), when staged
+  unsigned short* order;       // live list: sr at position p, kDead once removed
+  unsigned short* champIn;     // champion entering each position ...
+  unsigned short* champInPos;  // ... and the position it sits at
+  unsigned short* perm;        // sr -> job index within the round
+  float* lenT;                 // [CH][Jp]: len(sr, w), w = 1..CH
+  long long* red;              // [4]
+  // sort scratch, aliased over rem/L/Rr/r (16 bytes per job)
+  int64_t* khi;
+  int32_t* klo;
+  int* perm32;
 };
 
-__global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int tableInSmem) {
+__global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int CH) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   AfslSmem sm;
   {
     unsigned char* p = smem_raw;
-    sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Jp;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
-    sm.klo = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
-    sm.order = reinterpret_cast<int*>(p); p += 4 * (size_t)Jp;
-    sm.champIn = reinterpret_cast<int*>(p); p += 4 * (size_t)Jp;
-    sm.champInPos = reinterpret_cast<int*>(p); p += 4 * (size_t)Jp;
-    sm.r = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
-    sm.mx = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
+    sm.khi = reinterpret_cast<int64_t*>(p);
+    sm.klo = reinterpret_cast<int32_t*>(p + 8 * (size_t)Jp);
+    sm.perm32 = reinterpret_cast<int*>(p + 12 * (size_t)Jp);
     sm.rem = reinterpret_cast<float*>(p); p += 4 * (size_t)Jp;
     sm.L = reinterpret_cast<float*>(p); p += 4 * (size_t)Jp;
     sm.Rr = reinterpret_cast<float*>(p); p += 4 * (size_t)Jp;
-    sm.lenT = reinterpret_cast<float*>(p);
+    sm.r = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
+    sm.mx = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
+    sm.lenT = reinterpret_cast<float*>(p); p += 4 * (size_t)Jp * (size_t)CH;
+    sm.order = reinterpret_cast<unsigned short*>(p); p += 2 * (size_t)Jp;
+    sm.champIn = reinterpret_cast<unsigned short*>(p); p += 2 * (size_t)Jp;
+    sm.champInPos = reinterpret_cast<unsigned short*>(p); p += 2 * (size_t)Jp;
+    sm.perm = reinterpret_cast<unsigned short*>(p);
   }
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int W = a.stride;
@@ -77,38 +91,44 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
       continue;
     }
     __syncthreads();
-    auto S = [&](int i, int g) -> float {  // Info.Speedup[fmt.Sprint(g)], map miss => 0
+    auto S = [&](int job, int g) -> float {  // Info.Speedup[fmt.Sprint(g)], map miss => 0
       if (g < 0 || g >= W) return 0.0f;
-      return a.speedup[(size_t)(o + i) * (size_t)W + (size_t)g];
+      return a.speedup[(size_t)(o + job) * (size_t)W + (size_t)g];
     };
+    // ---- stable sort by SubmitTime (:42-44), then relabel every job by its sorted position
     for (int i = tid; i < n; i += kThreads) {
       sm.khi[i] = a.submit_sec[o + i];
       sm.klo[i] = a.submit_nsec ? a.submit_nsec[o + i] : 0;
-      sm.r[i] = 0;
-      sm.mx[i] = a.max_proc[o + i];
-      sm.rem[i] = a.remaining_sec[o + i];
-      const float s0 = S(i, 0), s1 = S(i, 1);
-      const float d = s1 - s0;
-      sm.L[i] = d / s1;
-      sm.Rr[i] = d / s0;
-    }
-    if (tableInSmem) {
-      const float* src = a.speedup + (size_t)o * (size_t)W;
-      for (int x = tid; x < n * W; x += kThreads) {
-        const int i = x / W, w = x - i * W;
-        sm.lenT[x] = w == 0 ? INF : a.remaining_sec[o + i] / src[x];  // afsl.go:94-100
-      }
     }
     __syncthreads();
-    block_argsort(sm.khi, sm.klo, sm.order, n, next_pow2(n > 0 ? n : 1));  // :42-44
+    block_argsort(sm.khi, sm.klo, sm.perm32, n, next_pow2(n > 0 ? n : 1));
+    for (int t = tid; t < n; t += kThreads) sm.perm[t] = (unsigned short)sm.perm32[t];
+    __syncthreads();  // the sort scratch is dead from here on
+    for (int t = tid; t < n; t += kThreads) {
+      const int j = sm.perm[t];
+      sm.rem[t] = a.remaining_sec[o + j];
+      sm.r[t] = 0;
+      sm.mx[t] = a.max_proc[o + j];
+      const float s0 = S(j, 0), s1 = S(j, 1);
+      const float d = s1 - s0;
+      sm.L[t] = d / s1;
+      sm.Rr[t] = d / s0;
+      sm.order[t] = (unsigned short)t;
+    }
+    for (int x = tid; x < n * CH; x += kThreads) {
+      const int t = x / CH, w = x - t * CH + 1;
+      const int j = sm.perm[t];
+      sm.lenT[(size_t)(w - 1) * Jp + t] = a.remaining_sec[o + j] / S(j, w);  // afsl.go:94-100
+    }
     __syncthreads();
 
     if (warp == 0) {
-      // len(x, w) for w given; w >= W is a map miss: rem / 0
+      // len(x, w): hot columns from shared memory, the rest divided on the fly (w >= W is a
+      // map miss: rem / 0)
       auto LEN = [&](int x, int w) -> float {
         if (w == 0) return INF;
-        if (w < 0 || w >= W) return sm.rem[x] / 0.0f;
-        return tableInSmem ? sm.lenT[x * W + w] : sm.rem[x] / S(x, w);
+        if (w <= CH) return sm.lenT[(size_t)(w - 1) * Jp + x];
+        return sm.rem[x] / S(sm.perm[x], w);
       };
       int len = n;        // entries in order[] (live + dead)
       int dead = 0;
@@ -121,29 +141,31 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
       while (free > 0 && nlive > 0) {  // :47
         // ---- topPriority: fold from startPos ------------------------------------------
         if (champ < 0) {
-          while (head < len && sm.order[head] < 0) head++;
+          while (head < len && sm.order[head] == kDead) head++;
           champ = sm.order[head];
           champPos = head;
           startPos = head + 1;
         }
+        // champion state, uniform across the warp
         int c = champ, cp = champPos;
+        int rc = sm.r[c];
+        float remc = sm.rem[c], Lc = sm.L[c], Rc = sm.Rr[c];
+        float lenA = LEN(c, rc);
         for (int base = startPos & ~31; base < len; base += 32) {
           const int p = base + lane;
-          const int jb = (p < len && p >= startPos) ? sm.order[p] : -1;
-          bool pend = jb >= 0;
+          const int jb = (p < len && p >= startPos) ? (int)sm.order[p] : (int)kDead;
+          bool pend = jb != kDead;
           // challenger-side values (independent of the champion)
           int rj = 0;
-          float remj = 0.f, Lj = 0.f, Rj = 0.f;
+          float remj = 0.f, Lj = 0.f, Rj = 0.f, selfLen = 0.f;
           if (pend) {
             rj = sm.r[jb];
             remj = sm.rem[jb];
             Lj = sm.L[jb];
             Rj = sm.Rr[jb];
+            selfLen = LEN(jb, rj);
           }
           while (true) {
-            const int rc = sm.r[c];
-            const float remc = sm.rem[c], Lc = sm.L[c], Rc = sm.Rr[c];
-            const float lenA = LEN(c, rc);
             bool beat = false;
             if (pend) {
               if (rc == 0 && rj == 0) {
@@ -161,35 +183,41 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
             const unsigned m = __ballot_sync(full, beat);
             if (!m) {
               if (pend) {
-                sm.champIn[p] = c;
-                sm.champInPos[p] = cp;
+                sm.champIn[p] = (unsigned short)c;
+                sm.champInPos[p] = (unsigned short)cp;
               }
               break;
             }
             const int f = __ffs(m) - 1;
             if (pend && lane <= f) {
-              sm.champIn[p] = c;
-              sm.champInPos[p] = cp;
+              sm.champIn[p] = (unsigned short)c;
+              sm.champInPos[p] = (unsigned short)cp;
               pend = false;
             }
+            // lane f becomes the champion: its whole state comes over by shuffle
             c = __shfl_sync(full, jb, f);
             cp = base + f;
+            rc = __shfl_sync(full, rj, f);
+            remc = __shfl_sync(full, remj, f);
+            Lc = __shfl_sync(full, Lj, f);
+            Rc = __shfl_sync(full, Rj, f);
+            lenA = __shfl_sync(full, selfLen, f);
           }
         }
         // ---- give it one GPU (:49-57) ----------------------------------------------------
         const int w = c, wpos = cp;
         __syncwarp();
-        const int nr = sm.r[w] + 1;
+        const int nr = rc + 1;
         free -= 1;
         const bool removed = nr >= sm.mx[w];
-        __syncwarp();
         if (lane == 0) {
           sm.r[w] = nr;
-          const float s0 = S(w, nr), s1 = S(w, nr + 1);
+          const int job = sm.perm[w];
+          const float s0 = S(job, nr), s1 = S(job, nr + 1);
           const float d = s1 - s0;
           sm.L[w] = d / s1;
           sm.Rr[w] = d / s0;
-          if (removed) sm.order[wpos] = -1;
+          if (removed) sm.order[wpos] = kDead;
         }
         if (removed) {
           nlive--;
@@ -210,11 +238,11 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
           int outp = 0;
           for (int base = 0; base < len; base += 32) {
             const int p = base + lane;
-            const int v = p < len ? sm.order[p] : -1;
-            const unsigned keep = __ballot_sync(full, v >= 0);
+            const int v = p < len ? (int)sm.order[p] : (int)kDead;
+            const unsigned keep = __ballot_sync(full, v != kDead);
             const int dst = outp + __popc(keep & ((1u << lane) - 1u));
             __syncwarp();
-            if (v >= 0) sm.order[dst] = v;
+            if (v != kDead) sm.order[dst] = (unsigned short)v;
             outp += __popc(keep);
             __syncwarp();
           }
@@ -226,30 +254,36 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
       }
     }
     __syncthreads();
-    for (int i = tid; i < n; i += kThreads) a.out_gpus[o + i] = sm.r[i];
+    for (int t = tid; t < n; t += kThreads) a.out_gpus[o + sm.perm[t]] = sm.r[t];
     __syncthreads();
     const int v = block_validate(a, o, n, total, a.out_gpus + o, nullptr, sm.red);  // deferred :39
     if (tid == 0) a.out_status[rd] = v;
   }
 }
 
-size_t afsl_fixed_smem(int Jp) { return (size_t)Jp * (8 + 4 * 10) + 8 * 4 + 32; }
+// shared memory: 28 bytes per job + the hot len() columns
+size_t afsl_fixed_smem(int Jp) { return (size_t)Jp * 28 + 8 * 4 + 32; }
+
+int afsl_hot_columns(const AllocArgs& a, int Jp) {
+  // as many columns as still leave room for 4 CTAs per SM (about 55 KB each), at most W - 1
+  const long budget = 55 * 1024;
+  long ch = (budget - (long)afsl_fixed_smem(Jp)) / (4L * Jp);
+  if (ch < 0) ch = 0;
+  if (ch > a.stride - 1) ch = a.stride - 1;
+  return (int)ch;
+}
 
 }  // namespace
 
 size_t afsl_smem_bytes(const AllocArgs& a) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  size_t fixed = afsl_fixed_smem(Jp);
-  size_t table = (size_t)a.max_jobs * (size_t)a.stride * 4;
-  return fixed + (fixed + table <= 220 * 1024 ? table : 0);
+  return afsl_fixed_smem(Jp) + (size_t)afsl_hot_columns(a, Jp) * 4 * (size_t)Jp;
 }
 
 cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  const size_t fixed = afsl_fixed_smem(Jp);
-  const size_t table = (size_t)a.max_jobs * (size_t)a.stride * 4;
-  const bool in = fixed + table <= 220 * 1024;
-  const size_t smem = fixed + (in ? table : 0);
+  const int CH = afsl_hot_columns(a, Jp);
+  const size_t smem = afsl_fixed_smem(Jp) + (size_t)CH * 4 * (size_t)Jp;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(afsl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -260,7 +294,7 @@ cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream) {
   if (perSm < 1) perSm = 1;
   int grid = sms * perSm;
   if (a.rounds < grid) grid = a.rounds;
-  afsl_kernel<<<grid, kThreads, smem, stream>>>(a, Jp, in ? 1 : 0);
+  afsl_kernel<<<grid, kThreads, smem, stream>>>(a, Jp, CH);
   return cudaGetLastError();
 }
 
