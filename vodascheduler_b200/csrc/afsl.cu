@@ -25,7 +25,7 @@
 //     is small) divide on the fly from the table in HBM; the two evaluate() ratios of a job are
 //     recomputed only when its count changes.
 // The dependent chain (picks x fold steps) is the cost; throughput comes from rounds in flight,
-// so shared memory per round is kept small (28 bytes per job + CH * 4) to fit 4 CTAs per SM.
+// so shared memory per round is kept small (32 bytes per job + CH * 4) to fit 4 CTAs per SM.
 // Jobs are relabelled by their sorted position; removal at max keeps order (lazy deletion +
 // periodic compaction of the live list).
 #include "common.cuh"
@@ -42,6 +42,7 @@ struct AfslSmem {
   float* rem;
   float* L;    // (S[r+1]-S[r]) / S[r+1]   "as the longer job"
   float* Rr;   // (S[r+1]-S[r]) / S[r]     "as the shorter job"
+  float* self; // len(job, r[job]): its own length at its own count (the champion's lenA)
   int32_t* r;
   int32_t* mx;
   unsigned short* order;       // live list: sr at position p, kDead once removed
@@ -70,6 +71,7 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
     sm.Rr = reinterpret_cast<float*>(p); p += 4 * (size_t)Jp;
     sm.r = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
     sm.mx = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
+    sm.self = reinterpret_cast<float*>(p); p += 4 * (size_t)Jp;
     sm.lenT = reinterpret_cast<float*>(p); p += 4 * (size_t)Jp * (size_t)CH;
     sm.order = reinterpret_cast<unsigned short*>(p); p += 2 * (size_t)Jp;
     sm.champIn = reinterpret_cast<unsigned short*>(p); p += 2 * (size_t)Jp;
@@ -113,6 +115,7 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
       const float d = s1 - s0;
       sm.L[t] = d / s1;
       sm.Rr[t] = d / s0;
+      sm.self[t] = INF;  // len(x, 0)
       sm.order[t] = (unsigned short)t;
     }
     for (int x = tid; x < n * CH; x += kThreads) {
@@ -150,20 +153,19 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
         int c = champ, cp = champPos;
         int rc = sm.r[c];
         float remc = sm.rem[c], Lc = sm.L[c], Rc = sm.Rr[c];
-        float lenA = LEN(c, rc);
+        float lenA = sm.self[c];
         for (int base = startPos & ~31; base < len; base += 32) {
           const int p = base + lane;
           const int jb = (p < len && p >= startPos) ? (int)sm.order[p] : (int)kDead;
           bool pend = jb != kDead;
           // challenger-side values (independent of the champion)
           int rj = 0;
-          float remj = 0.f, Lj = 0.f, Rj = 0.f, selfLen = 0.f;
+          float remj = 0.f, Lj = 0.f, Rj = 0.f;
           if (pend) {
             rj = sm.r[jb];
             remj = sm.rem[jb];
             Lj = sm.L[jb];
             Rj = sm.Rr[jb];
-            selfLen = LEN(jb, rj);
           }
           while (true) {
             bool beat = false;
@@ -201,7 +203,7 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
             remc = __shfl_sync(full, remj, f);
             Lc = __shfl_sync(full, Lj, f);
             Rc = __shfl_sync(full, Rj, f);
-            lenA = __shfl_sync(full, selfLen, f);
+            lenA = sm.self[c];  // uniform broadcast read
           }
         }
         // ---- give it one GPU (:49-57) ----------------------------------------------------
@@ -217,6 +219,7 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
           const float d = s1 - s0;
           sm.L[w] = d / s1;
           sm.Rr[w] = d / s0;
+          sm.self[w] = sm.rem[w] / s0;  // len(w, nr) = rem / S[nr] (afsl.go:98)
           if (removed) sm.order[wpos] = kDead;
         }
         if (removed) {
@@ -261,8 +264,8 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
   }
 }
 
-// shared memory: 28 bytes per job + the hot len() columns
-size_t afsl_fixed_smem(int Jp) { return (size_t)Jp * 28 + 8 * 4 + 32; }
+// shared memory: 32 bytes per job + the hot len() columns
+size_t afsl_fixed_smem(int Jp) { return (size_t)Jp * 32 + 8 * 4 + 32; }
 
 int afsl_hot_columns(const AllocArgs& a, int Jp) {
   // as many columns as still leave room for 4 CTAs per SM (about 55 KB each), at most W - 1
