@@ -92,6 +92,31 @@ def test_ffdl_full_size_rounds(ctx, oracle):
     assert (per_round <= 1024).all() and (per_round > 900).all()
 
 
+def test_afsl_full_size_rounds(ctx, oracle):
+    """BASELINE config 3 shape (1024 jobs x 4096 GPUs): a sample against the oracle, plus the
+    size-independent properties (every GPU handed out, nobody above max)."""
+    b = synth.jobs_batch("AFS-L", rounds=24, jobs_per_round=1024, total_gpu=4096)
+    g, s = _same(ctx, oracle, b)
+    assert (s == 0).all()
+    per_round = g.reshape(24, 1024).sum(1)
+    assert (per_round == 4096).all()
+    assert (g <= b.max_proc).all() and (g >= 0).all()
+
+
+def test_tiresias_c1_shape(ctx, oracle):
+    """BASELINE config 0 shape: 64 jobs on 16 GPUs, many rounds, against the string-map oracle."""
+    b = synth.jobs_batch("ElasticTiresias", rounds=400, jobs_per_round=64, total_gpu=16)
+    g, s = _same(ctx, oracle, b, dense=False, threads=8)
+    assert (g.reshape(400, 64).sum(1) <= 16).all()
+
+
+def test_esrjf_large_rounds(ctx, oracle):
+    """The policy of BASELINE config 4 at 1024 jobs per round (bitonic sort + epoch fill)."""
+    for algo in ("ElasticSRJF", "ElasticFIFO"):
+        b = synth.jobs_batch(algo, rounds=64, jobs_per_round=1024, total_gpu=3000)
+        _same(ctx, oracle, b)
+
+
 def test_ffdl_wide_max_and_table_edge(ctx, oracle):
     """max_proc beyond the dense table (map miss => S = 0) and beyond 255 (uint16 SOL path)."""
     b = synth.jobs_batch("FfDLOptimizer", rounds=12, jobs_per_round=24, total_gpu=700)

@@ -166,23 +166,34 @@ class PlacementManager:
 
     # placement_manager.go:306-332
     def Place(self, jobRequests: Dict[str, int]) -> List[str]:
+        batch = self.begin_place(jobRequests)
+        out = self._context().place(batch)
+        return self.finish_place(jobRequests, out, 0)
+
+    def begin_place(self, jobRequests: Dict[str, int]) -> PlaceBatch:
+        """releaseSlots + the round as a PlaceBatch (first half of Place)."""
         self.releaseSlots(jobRequests)
+        return self.pack(jobRequests)
+
+    def finish_place(self, jobRequests: Dict[str, int], out, rnd: int, node_base: int = 0,
+                     entry_base: int = 0) -> List[str]:
+        """Second half of Place: apply round `rnd` of a (possibly batched) voda_place result.
+        node_base / entry_base locate the round inside the batch's flat output arrays."""
+        if out.status[rnd] != 0:
+            from ._lib import status_str
+            raise PlacementError(int(out.status[rnd]), status_str(out.status[rnd]))
         names = list(jobRequests)
         current = list(self.nodeStates.values())  # currentNodeList (:494-497)
-        out = self._context().place(self.pack(jobRequests))
-        if out.status[0] != 0:
-            from ._lib import status_str
-            raise PlacementError(int(out.status[0]), status_str(out.status[0]))
         n = len(current)
         # logical nodes filled by bestFit, then renamed to the physical node they bind to
         logical = [NewNodeState("TBD", nd.totalSlots) for nd in current]
-        for t in range(int(out.lay_cnt[0])):
+        for t in range(entry_base, entry_base + int(out.lay_cnt[rnd])):
             logical[int(out.lay_node[t])].jobNumWorkers[names[int(out.lay_job[t])]] = int(out.lay_workers[t])
         for i in range(n):
-            logical[i].freeSlots = int(out.free_slots[i])
-            logical[i].name = current[int(out.phys_of_logical[i])].name  # rename (:509-511)
-        self.lastScore = int(out.score[0])
-        self.lastCrossNode = int(out.cross[0])
+            logical[i].freeSlots = int(out.free_slots[node_base + i])
+            logical[i].name = current[int(out.phys_of_logical[node_base + i])].name  # rename (:509-511)
+        self.lastScore = int(out.score[rnd])
+        self.lastCrossNode = int(out.cross[rnd])
         self.nodeStates = {nd.name: nd for nd in logical}
         self.updateJobStates()
         return self.updatePodNodeName()
