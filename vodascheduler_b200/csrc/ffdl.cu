@@ -35,7 +35,7 @@ namespace {
 #define VODA_FFDL_CELLS 8
 #endif
 #ifndef VODA_FFDL_MINBLOCKS
-#define VODA_FFDL_MINBLOCKS 1
+#define VODA_FFDL_MINBLOCKS 12
 #endif
 // 64 threads x 8 cells (two tiles per thread at K = 1024) measured best on B200 among
 // {32,64,128} x {4,8,16,32}; see profiles/r1_ffdl_shape_sweep.txt
@@ -50,6 +50,8 @@ struct FfdlSmem {
   int32_t* klo;      // [Jp]
   int* perm;         // [Jp]
   int32_t* smax;     // [Jp]  max_proc in sorted order
+  int32_t* scum;     // [Jp]  min(K, sum of clamp(max_proc, 0, K) over the first j+1 sorted jobs)
+  float* srmax;      // [Jp]  max over the row's usable g of S_j[g] (-inf if none)
   long long* red;    // [2]
   int* misc;         // [4]
 };
@@ -195,6 +197,12 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, 
   if (J >= 1)
     for (int g = tid + 1; g <= SW; g += kThreads) sm.srow1[g - 1] = s_value(1, g);
   __syncthreads();
+  // Saturation: once k >= klim_j = sum of the first j jobs' max sizes, the GPU budget no longer
+  // binds, so P[j][k] is one constant c_j (and SOL[j][k] one constant) for every k >= klim_j —
+  // bit for bit, because each candidate S_j[g] + P[j-1][k-g] then adds the same two numbers.
+  // Tiles wholly beyond klim_j are filled with c_j instead of being computed, their SOL is
+  // not stored, and the backtrack reads SOL[j][min(k, klim_j)].
+  float cprev = 0.0f;  // c_0: P[0][k] = 0
   for (int j = 1; j <= J; j++) {
     const float* srow = (j & 1) ? sm.srow1 : sm.srow0;
     float* snext = (j & 1) ? sm.srow0 : sm.srow1;
@@ -212,8 +220,20 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, 
     const int gt = min(gmax, W - 1);
     const int nblk = gt > 0 ? (gt + 3) >> 2 : 0;
     SolT* solrow = reinterpret_cast<SolT*>(solSlab + (size_t)(j - 1) * solStride);
-    for (int tq = tid; tq < KT; tq += kThreads)
-      ffdl_row_tile<SolT>(prev, cur, srow, tq, nblk, max(W, 1), gmax, solrow);
+    const int klim = sm.scum[j - 1];
+    // c_j = max(-10000, max_g (S_j[g] + c_{j-1})) = max(-10000, (max_g S_j[g]) + c_{j-1}): rounding
+    // is monotone, so the maximum commutes with the addition exactly
+    const float ccur = fmaxf(-10000.0f, sm.srmax[j - 1] + cprev);
+    for (int tq = tid; tq < KT; tq += kThreads) {
+      if (kCells * tq + 1 > klim) {
+        const float4 c4 = make_float4(ccur, ccur, ccur, ccur);
+#pragma unroll
+        for (int i = 0; i < kCells / 4; i++) cur[(kCells / 4) * tq + 1 + i] = c4;
+      } else {
+        ffdl_row_tile<SolT>(prev, cur, srow, tq, nblk, max(W, 1), gmax, solrow);
+      }
+    }
+    cprev = ccur;
     if (tid == 0) cur[0] = make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, -10000.0f);  // P[j][0]
     if (j < J) {
 #pragma unroll
@@ -242,6 +262,7 @@ struct FfdlMeta {
 struct FfdlScratch {
   FfdlMeta* meta;      // [count]
   int32_t* perm;       // [count][Jcap] sorted position -> job index within the round
+  int32_t* klim;       // [count][Jcap] saturation point of each DP row
   unsigned char* sol;  // [count][Jcap][solStride]
   size_t slabBytes;    // Jcap * solStrideMax
   int Jcap;
@@ -264,6 +285,8 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS) ffdl_dp_kernel(
     sm.klo = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
     sm.perm = reinterpret_cast<int*>(p); p += sizeof(int) * (size_t)Jp;
     sm.smax = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
+    sm.scum = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
+    sm.srmax = reinterpret_cast<float*>(p); p += sizeof(float) * (size_t)Jp;
     sm.misc = reinterpret_cast<int*>(p);
   }
   const int tid = threadIdx.x;
@@ -306,11 +329,27 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS) ffdl_dp_kernel(
       const int mx = a.max_proc[o + pj];
       sm.smax[j] = mx;
       lmax = max(lmax, mx);
+      // largest speedup value the row can use (g beyond the table reads 0: a Go map miss)
+      const int gmx = min(mx, K);
+      float rm = gmx >= max(a.stride, 1) ? 0.0f : VODA_NEG_INF;
+      const float* sj = a.speedup + (size_t)(o + pj) * (size_t)a.stride;
+      for (int g = 1; g <= min(gmx, a.stride - 1); g++) rm = fmaxf(rm, sj[g]);
+      sm.srmax[j] = rm;
     }
     if (tid == 0) sm.misc[0] = 0;
     __syncthreads();
     for (int d = 16; d > 0; d >>= 1) lmax = max(lmax, __shfl_xor_sync(0xffffffffu, lmax, d));
     if ((tid & 31) == 0) atomicMax(&sm.misc[0], lmax);
+    if (tid == 0) {  // running sum of the usable sizes, clipped to K (a short serial scan)
+      long long acc = 0;
+      int32_t* gklim = sc.klim + (size_t)rr * sc.Jcap;
+      for (int j = 0; j < J; j++) {
+        acc += max(0, min(sm.smax[j], K));
+        const int kl = (int)min(acc, (long long)K);
+        sm.scum[j] = kl;
+        gklim[j] = kl;
+      }
+    }
     __syncthreads();
     const int gmaxRound = min(sm.misc[0], K);
     // 3-4. DP rows
@@ -356,13 +395,15 @@ __global__ void __launch_bounds__(kBtThreads) ffdl_backtrack_kernel(AllocArgs a,
   if (meta.st == VODA_ST_OK && lane == 0) {
     const unsigned char* slab = sc.sol + (size_t)rr * sc.slabBytes;
     const int32_t* gperm = sc.perm + (size_t)rr * sc.Jcap;
+    const int32_t* gklim = sc.klim + (size_t)rr * sc.Jcap;
     const size_t stride = (size_t)K4cap * 4 * (size_t)meta.elem;
     int k = meta.K;
     for (int j = meta.J; j > 0; j--) {
       int g = 0;  // SOL[j][0] == 0
-      if (k > 0) {
+      const int kk = min(k, gklim[j - 1]);  // SOL[j][k] is constant from the row's saturation point on
+      if (kk > 0) {
         const unsigned char* row = slab + (size_t)(j - 1) * stride;
-        g = meta.elem == 1 ? (int)row[k - 1] : (int)reinterpret_cast<const uint16_t*>(row)[k - 1];
+        g = meta.elem == 1 ? (int)row[kk - 1] : (int)reinterpret_cast<const uint16_t*>(row)[kk - 1];
       }
       a.out_gpus[o + gperm[j - 1]] = g;
       k -= g;
@@ -401,7 +442,7 @@ static void ffdl_shape(const AllocArgs& a, int* K4cap, int* SW, int* Jp, size_t*
   *SW = (sw + 3) & ~3;
   *Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
   *smem = sizeof(float4) * 2 * (size_t)(*K4cap + 1) + sizeof(float) * 2 * (size_t)(*SW) +
-          (sizeof(int64_t) + 3 * sizeof(int32_t)) * (size_t)(*Jp) + 2 * sizeof(long long) + 4 * sizeof(int);
+          (sizeof(int64_t) + 5 * sizeof(int32_t)) * (size_t)(*Jp) + 2 * sizeof(long long) + 4 * sizeof(int);
 }
 
 static size_t ffdl_jcap(const AllocArgs& a) {
@@ -415,7 +456,7 @@ size_t ffdl_scratch_per_round(const AllocArgs& a) {
   size_t smem;
   ffdl_shape(a, &K4cap, &SW, &Jp, &smem);
   const size_t Jcap = ffdl_jcap(a);
-  return Jcap * (size_t)K4cap * 8 + ((Jcap * 4 + 15) & ~(size_t)15) + sizeof(FfdlMeta);
+  return Jcap * (size_t)K4cap * 8 + 2 * ((Jcap * 4 + 15) & ~(size_t)15) + sizeof(FfdlMeta);
 }
 
 size_t ffdl_smem_bytes(const AllocArgs& a) {
@@ -443,7 +484,8 @@ cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* sc
   sc.Jcap = (int)(permRow / 4);
   sc.sol = base;
   sc.perm = reinterpret_cast<int32_t*>(base + (size_t)count * sc.slabBytes);
-  sc.meta = reinterpret_cast<FfdlMeta*>(base + (size_t)count * (sc.slabBytes + permRow));
+  sc.klim = reinterpret_cast<int32_t*>(base + (size_t)count * (sc.slabBytes + permRow));
+  sc.meta = reinterpret_cast<FfdlMeta*>(base + (size_t)count * (sc.slabBytes + 2 * permRow));
   int perSm = 0;
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, ffdl_dp_kernel, kThreads, smem);
   if (e != cudaSuccess) return e;
