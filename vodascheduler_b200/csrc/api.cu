@@ -488,12 +488,14 @@ static PlaceArgs make_place_args(const voda_place_batch* b, const voda_place_out
   return a;
 }
 
-static int dispatch_place(voda_ctx* ctx, const PlaceArgs& a, cudaStream_t stream) {
+static int dispatch_place(voda_ctx* ctx, const PlaceArgs& a, DevBuf& scratch, cudaStream_t stream) {
   if (a.rounds == 0) return VODA_OK;
   if (a.max_nodes > 128) return fail(ctx, VODA_E_UNSUPPORTED, "placement: more than 128 nodes per round");
   if (place_smem_bytes(a) > 220 * 1024)
     return fail(ctx, VODA_E_UNSUPPORTED, "placement: too many requests per round for one CTA's shared memory");
-  CU(launch_place(a, ctx->sms, stream));
+  int rc = ensure(ctx, scratch, place_scratch_bytes(a, ctx->sms), stream);
+  if (rc) return rc;
+  CU(launch_place(a, ctx->sms, scratch.p, stream));
   ctx->launches += 1;
   return VODA_OK;
 }
@@ -506,7 +508,7 @@ int voda_place_dev(voda_ctx* ctx, const voda_place_batch* b, const voda_place_ou
   CU(cudaSetDevice(ctx->device));
   PlaceArgs a = make_place_args(b, o);
   if (a.max_requests < 1) a.max_requests = 1;
-  return dispatch_place(ctx, a, ctx->stream);
+  return dispatch_place(ctx, a, ctx->scratch, ctx->stream);
 }
 
 int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o) {
@@ -560,7 +562,7 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   a.phys_of_logical = (int32_t*)(base + o_ph); a.free_slots = (int32_t*)(base + o_fr); a.lay_cnt = (int32_t*)(base + o_lc);
   a.lay_node = (int32_t*)(base + o_ln); a.lay_job = (int32_t*)(base + o_lj); a.lay_workers = (int32_t*)(base + o_lw);
   a.score = (long long*)(base + o_sc); a.cross = (int32_t*)(base + o_cr); a.status = (int32_t*)(base + o_st);
-  rc = dispatch_place(ctx, a, s);
+  rc = dispatch_place(ctx, a, ctx->pipe_scratch[0], s);
   if (rc) return rc;
   auto d2h = [&](void* dst, size_t at, size_t bytes) -> cudaError_t {
     return (bytes && dst) ? cudaMemcpyAsync(dst, base + at, bytes, cudaMemcpyDeviceToHost, s) : cudaSuccess;

@@ -32,6 +32,7 @@ cudaError_t launch_munkres(int n, int batch, const int64_t* A, int32_t* out, int
 
 // bestFit + score + munkres placement rounds (place.cu)
 size_t place_smem_bytes(const PlaceArgs& a);
-cudaError_t launch_place(const PlaceArgs& a, int sms, cudaStream_t stream);
+size_t place_scratch_bytes(const PlaceArgs& a, int sms);
+cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream);
 
 }  // namespace voda

@@ -6,24 +6,26 @@
 //   rename + score     :509-512
 // One CTA per round.  Warp 0 runs bestFit (a serial walk over the sorted requests; the two
 // node searches per step are warp reductions over (freeSlots, index) keys that keep the
-// reference's first-index tie-breaks), all threads build the n x n score matrix in shared
-// memory with atomics (a join of the new layout and the previous one on the job id), then
-// warp 0 solves the assignment in place.  Reference quirks kept: the last chunk of a split job
-// records the WHOLE request (Q11, :479) so freeSlots can go negative, and the loop that never
-// ends once a request meets a cluster without usable slots (Q12) is cut with
-// VODA_ST_NONTERMINATING.
+// reference's first-index tie-breaks), all threads build the n x n score matrix with atomics
+// (a join of the new layout and the previous one on the job id), then warp 0 solves the
+// assignment in place.  The matrix lives in an L2-resident per-CTA slab of global scratch, not
+// in shared memory: bestFit and the solve are single-warp dependent chains, so throughput comes
+// from resident rounds per SM, and 64 KB of shared memory per round would allow only two.
+// Reference quirks kept: the last chunk of a split job records the WHOLE request (Q11, :479)
+// so freeSlots can go negative, and the loop that never ends once a request meets a cluster
+// without usable slots (Q12) is cut with VODA_ST_NONTERMINATING.
 #include "kernels.h"
 #include "munkres.cuh"
 
 namespace voda {
 namespace {
 
-constexpr int kThreads = 128;
+constexpr int kThreads = 64;
 constexpr int kMaxNodes = 128;
 constexpr int kLimit = 1 << 22;  // |freeSlots| * 128 must fit an int32 key
 
 struct PlaceSmem {
-  int32_t* M;        // [n*n] scores, then rowmax - score
+  int32_t* M;        // [n*n] scores, then rowmax - score (global scratch slab of this CTA)
   int64_t* khi;      // [Mp] sort key (-workers)
   int32_t* klo;      // [Mp] zeros
   int* perm;         // [Mp]
@@ -38,13 +40,12 @@ struct PlaceSmem {
   MunkresSmem mk;
 };
 
-__global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp) {
+__global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, int32_t* slabs, size_t slabInts) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   PlaceSmem sm;
   {
     unsigned char* p = smem_raw;
-    sm.M = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)a.max_nodes * a.max_nodes;
-    p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
+    sm.M = slabs + (size_t)blockIdx.x * slabInts;
     sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Mp;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
     sm.mk.ra = p; p += 8 * 128;
@@ -294,29 +295,47 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp) {
   }
 }
 
-size_t place_smem(int maxNodes, int Mp) {
-  return 4 * (size_t)maxNodes * maxNodes + 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 8 * 128 +
+size_t place_smem(int Mp) {
+  return 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 8 * 128 +
          4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 4 * 4 * 128 + 16 + 64;
 }
 
 }  // namespace
 
-size_t place_smem_bytes(const PlaceArgs& a) { return place_smem(a.max_nodes, next_pow2(a.max_requests > 0 ? a.max_requests : 1)); }
+size_t place_smem_bytes(const PlaceArgs& a) { return place_smem(next_pow2(a.max_requests > 0 ? a.max_requests : 1)); }
 
-cudaError_t launch_place(const PlaceArgs& a, int sms, cudaStream_t stream) {
+static size_t place_slab_ints(const PlaceArgs& a) { return (((size_t)a.max_nodes * a.max_nodes) + 63) & ~(size_t)63; }
+
+static int place_grid(const PlaceArgs& a, int sms, size_t smem, cudaError_t* err) {
+  int perSm = 0;
+  *err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, place_kernel, kThreads, smem);
+  if (perSm < 1) perSm = 1;
+  int grid = sms * perSm;
+  if (a.rounds < grid) grid = a.rounds;
+  return grid;
+}
+
+// bytes of global scratch the launch needs (score-matrix slabs, one per CTA)
+size_t place_scratch_bytes(const PlaceArgs& a, int sms) {
   const int Mp = next_pow2(a.max_requests > 0 ? a.max_requests : 1);
-  const size_t smem = place_smem(a.max_nodes, Mp);
+  const size_t smem = place_smem(Mp);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e;
+  const int grid = place_grid(a, sms, smem, &e);
+  return (size_t)grid * place_slab_ints(a) * 4;
+}
+
+cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream) {
+  const int Mp = next_pow2(a.max_requests > 0 ? a.max_requests : 1);
+  const size_t smem = place_smem(Mp);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  int perSm = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, place_kernel, kThreads, smem);
+  cudaError_t e;
+  const int grid = place_grid(a, sms, smem, &e);
   if (e != cudaSuccess) return e;
-  if (perSm < 1) perSm = 1;
-  int grid = sms * perSm;
-  if (a.rounds < grid) grid = a.rounds;
-  place_kernel<<<grid, kThreads, smem, stream>>>(a, Mp);
+  place_kernel<<<grid, kThreads, smem, stream>>>(a, Mp, static_cast<int32_t*>(scratch), place_slab_ints(a));
   return cudaGetLastError();
 }
 
