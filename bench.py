@@ -389,10 +389,20 @@ def main():
         ab = alg_bytes(wl)
         roof = None
         if ab is not None:
-            kernel_ms = ms / args.steps  # one kernel per step: the launch IS the step
+            # the step is the dominant kernel plus (FfDL only) its small backtrack launch, ~10 % of the
+            # step in the ncu launch list (profiles/r1_final_launches.csv): the step time is used as
+            # the launch time, which can only understate the achieved figure
+            kernel_ms = ms / args.steps
             ach = ab / (kernel_ms / 1e3) / 1e9
+            traffic = None
+            tpath = os.path.join(ROOT, "profiles", "r1_traffic.json")
+            if os.path.exists(tpath):  # DRAM bytes of the dominant kernel from the committed ncu capture
+                with open(tpath) as f:
+                    t = json.load(f).get(args.workload)
+                if t:
+                    traffic = t["bytes_per_round"] * R
             roof = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                    "traffic": None, "peak_source": peak_src, "kernel": f"{wl.get('algo', wl['kind'])} batch kernel",
+                    "traffic": traffic, "peak_source": peak_src, "kernel": f"{wl.get('algo', wl['kind'])} batch kernel",
                     "algorithmic_bytes_per_launch": ab,
                     "note": "compute/latency-bound path: HBM fraction is low by nature (SURVEY 8d); see profiles/"}
         cpu = None
