@@ -95,8 +95,9 @@ def jobs_batch(algo, rounds, jobs_per_round, total_gpu, seed=SEED, *, force_min1
 
 
 def quirk_batch(algo, rounds, jobs_per_round, total_gpu, seed=SEED + 1):
-    """D.1 plus the reference's sharp edges: min == max, min > max, Priority 2, zero total,
-    tie-heavy keys, flat curves (zero / negative gains), ragged job counts."""
+    """D.1 plus the reference's sharp edges: min == max, min > max, Priority 2, zero and
+    negative totals, negative minimum, tie-heavy keys, flat curves (zero / negative gains),
+    ragged job counts."""
     b = jobs_batch(algo, rounds, jobs_per_round, total_gpu, seed, ragged=True, force_min1=False)
     n = b.jobs
     rnd = np.repeat(np.arange(rounds, dtype=np.int64), np.diff(b.job_off))
@@ -121,7 +122,10 @@ def quirk_batch(algo, rounds, jobs_per_round, total_gpu, seed=SEED + 1):
     tg = np.asarray(b.total_gpu).copy()
     tg[ru < 0.05] = 0
     tg[(ru >= 0.05) & (ru < 0.15)] = 1 + (tg[(ru >= 0.05) & (ru < 0.15)] // 7)
+    tg[(ru >= 0.15) & (ru < 0.18)] = -1                      # negative total -> "exceeded total GPUs"
     b.total_gpu = tg.astype(np.int32)
+    neg = _u(seed, rnd, job, 9) < 0.004                      # negative minimum -> "can't be negative"
+    b.min_proc = np.where(neg, -1, b.min_proc).astype(np.int32)
     return b
 
 
