@@ -140,3 +140,20 @@ def test_declared_bounds_are_enforced(ctx):
     b.max_jobs = 8
     g, s = ctx.allocate(b)
     assert (s == 8).all() and (g == 0).all()
+
+
+def test_ffdl_packed_rows_opt_in(oracle, monkeypatch):
+    """VODA_PACK_ROWS=1: the host path ships only the speedup entries FfDL can read (packed
+    rows + offsets); results must not change."""
+    from vodascheduler_b200 import Context
+    monkeypatch.setenv("VODA_PACK_ROWS", "1")
+    monkeypatch.setenv("VODA_HOST_THREADS", "3")
+    c = Context(0)
+    try:
+        for b in (synth.jobs_batch("FfDLOptimizer", rounds=4000, jobs_per_round=40, total_gpu=90, ragged=True),
+                  synth.quirk_batch("FfDLOptimizer", rounds=500, jobs_per_round=30, total_gpu=50)):
+            g_ref, s_ref = oracle.allocate(b, dense=True, threads=8)
+            g, s = c.allocate(b)
+            assert np.array_equal(s, s_ref) and np.array_equal(g, g_ref)
+    finally:
+        c.close()

@@ -11,7 +11,11 @@
 #include <string>
 #include <vector>
 
+#include <cstdlib>
+#include <memory>
+
 #include "common.cuh"
+#include "hostpack.h"
 #include "kernels.h"
 
 using namespace voda;
@@ -29,6 +33,11 @@ struct voda_ctx {
   DevBuf scratch;                  // kernel scratch for the main stream
   DevBuf pipe_scratch[2];          // kernel scratch per pipeline slot
   DevBuf stage[2];                 // staged inputs + outputs per pipeline slot
+  void* hstage[2] = {nullptr, nullptr};   // pinned host staging per slot (packed speedup rows)
+  size_t hstage_cap[2] = {0, 0};
+  cudaEvent_t h2d_done[2] = {nullptr, nullptr};  // the slot's host staging has been consumed
+  std::unique_ptr<HostPool> pool;  // host threads that pack rows (created on first use)
+  bool pack_rows = false;          // VODA_PACK_ROWS=1 enables the FfDL row packing (measured slower: DESIGN.md)
   int64_t launches = 0;
   std::string err;
 };
@@ -214,6 +223,9 @@ int voda_ctx_create(int device, voda_ctx** out) {
   if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
   for (int i = 0; i < 2; i++)
     if ((e = cudaStreamCreateWithFlags(&ctx->pipe[i], cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
+  for (int i = 0; i < 2; i++)
+    if ((e = cudaEventCreateWithFlags(&ctx->h2d_done[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if (const char* v = std::getenv("VODA_PACK_ROWS")) ctx->pack_rows = std::atoi(v) != 0;
   *out = ctx;
   return VODA_OK;
 }
@@ -225,6 +237,11 @@ void voda_ctx_destroy(voda_ctx* ctx) {
   DevBuf* bufs[] = {&ctx->scratch, &ctx->pipe_scratch[0], &ctx->pipe_scratch[1], &ctx->stage[0], &ctx->stage[1]};
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
+  for (int i = 0; i < 2; i++) {
+    if (ctx->hstage[i]) cudaFreeHost(ctx->hstage[i]);
+    if (ctx->h2d_done[i]) cudaEventDestroy(ctx->h2d_done[i]);
+  }
+  ctx->pool.reset();
   if (ctx->stream) cudaStreamDestroy(ctx->stream);
   for (int i = 0; i < 2; i++)
     if (ctx->pipe[i]) cudaStreamDestroy(ctx->pipe[i]);
@@ -375,12 +392,46 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     if (f & F_MIN) o_mn = in(b->min_proc, 4, j0, nj);
     if (f & F_MAX) o_mx = in(b->max_proc, 4, j0, nj);
     if (f & F_REM) o_rm = in(b->remaining_sec, 4, j0, nj);
-    if (f & F_SPEED) o_sp = in(b->speedup, 4 * W, j0, nj);
+    // FfDL, opt-in (VODA_PACK_ROWS=1): strip the dense rows down to the entries the DP can read
+    // (hostpack.h).  It cuts the PCIe bytes 2.7x but the strided host gather reads almost as
+    // many bytes from host DRAM as the DMA engine would have moved, more slowly: measured
+    // 10.1 ms vs 8.4 ms per 10k rounds on the 16-core box, so it is off by default
+    const bool packed = ctx->pack_rows && b->algo == VODA_ALGO_FFDL_OPTIMIZER && W >= 8 && nj > 0;
+    size_t o_spoff = 0, packed_floats = 0;
+    if (packed) {
+      if (!ctx->pool) {
+        int t = (int)std::thread::hardware_concurrency() / 2;
+        if (const char* v = std::getenv("VODA_HOST_THREADS")) t = std::atoi(v);
+        ctx->pool.reset(new HostPool(std::max(1, std::min(t, 8))));
+      }
+      const size_t need = 4 * (nj + 1) + 4 * W * nj + 256;
+      if (ctx->hstage_cap[slot] < need) {
+        CU(cudaStreamSynchronize(s));
+        if (ctx->hstage[slot]) CU(cudaFreeHost(ctx->hstage[slot]));
+        ctx->hstage[slot] = nullptr;
+        ctx->hstage_cap[slot] = 0;
+        CU(cudaHostAlloc(&ctx->hstage[slot], need + need / 8, cudaHostAllocDefault));
+        ctx->hstage_cap[slot] = need + need / 8;
+      } else {
+        CU(cudaEventSynchronize(ctx->h2d_done[slot]));  // the DMA of chunk c-2 has read this slot
+      }
+      int32_t* h_off = (int32_t*)ctx->hstage[slot];
+      float* h_sp = (float*)((char*)ctx->hstage[slot] + align256(4 * (nj + 1)));
+      packed_floats = ffdl_pack_rows(*ctx->pool, off, b->total_gpu, b->max_proc, b->speedup, (int)W, r0, r1,
+                                     h_off, h_sp, W * nj);
+      o_spoff = carve(4 * (nj + 1));
+      copies.push_back({o_spoff, h_off, 4 * (nj + 1)});
+      o_sp = carve(4 * packed_floats);
+      copies.push_back({o_sp, h_sp, 4 * packed_floats});
+    } else if (f & F_SPEED) {
+      o_sp = in(b->speedup, 4 * W, j0, nj);
+    }
     const size_t o_og = carve(4 * nj), o_os = carve(4 * nr);
     rc = ensure(ctx, ctx->stage[slot], pos, s);
     if (rc) return rc;
     char* base = (char*)ctx->stage[slot].p;
     for (const Copy& cp : copies) CU(cudaMemcpyAsync(base + cp.at, cp.src, cp.bytes, cudaMemcpyHostToDevice, s));
+    if (packed) CU(cudaEventRecord(ctx->h2d_done[slot], s));
     AllocArgs a = make_args(b);
     a.rounds = (int)nr;
     a.job_base = j0;
@@ -398,6 +449,7 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     a.max_proc = (f & F_MAX) ? (const int32_t*)(base + o_mx) : nullptr;
     a.remaining_sec = (f & F_REM) ? (const float*)(base + o_rm) : nullptr;
     a.speedup = (f & F_SPEED) ? (const float*)(base + o_sp) : nullptr;
+    a.sp_off = packed ? (const int32_t*)(base + o_spoff) : nullptr;
     a.out_gpus = (int32_t*)(base + o_og);
     a.out_status = (int32_t*)(base + o_os);
     rc = dispatch_alloc(ctx, a, ctx->pipe_scratch[slot], s);

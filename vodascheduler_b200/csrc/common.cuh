@@ -30,6 +30,9 @@ struct AllocArgs {
   const int32_t* max_proc;
   const float* remaining_sec;
   const float* speedup;
+  const int32_t* sp_off;  // null: dense table [job * stride + g].  Else PACKED rows (host path of
+                          // FfDL): entry g of job j is speedup[sp_off[j] + g], only the g the
+                          // policy can read are present
   int32_t stride;      // speedup table width W
   int32_t queue_num;   // TiresiasQueueNum
   int32_t compaction;  // ElasticTiresiasCompactionThreshold

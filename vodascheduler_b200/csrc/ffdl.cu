@@ -192,7 +192,9 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, 
     const int mx = sm.smax[j - 1];
     const int gt = min(min(mx, K), W - 1);  // last g served from the table loop
     if (g > gt) return VODA_NEG_INF;
-    return a.speedup[(size_t)(o + sm.perm[j - 1]) * (size_t)W + (size_t)g];
+    const int job = o + sm.perm[j - 1];
+    const size_t row = a.sp_off ? (size_t)a.sp_off[job] : (size_t)job * (size_t)W;
+    return a.speedup[row + (size_t)g];
   };
   if (J >= 1)
     for (int g = tid + 1; g <= SW; g += kThreads) sm.srow1[g - 1] = s_value(1, g);
@@ -332,7 +334,7 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS) ffdl_dp_kernel(
       // largest speedup value the row can use (g beyond the table reads 0: a Go map miss)
       const int gmx = min(mx, K);
       float rm = gmx >= max(a.stride, 1) ? 0.0f : VODA_NEG_INF;
-      const float* sj = a.speedup + (size_t)(o + pj) * (size_t)a.stride;
+      const float* sj = a.speedup + (a.sp_off ? (size_t)a.sp_off[o + pj] : (size_t)(o + pj) * (size_t)a.stride);
       for (int g = 1; g <= min(gmx, a.stride - 1); g++) rm = fmaxf(rm, sj[g]);
       sm.srmax[j] = rm;
     }
