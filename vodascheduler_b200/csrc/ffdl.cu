@@ -303,6 +303,7 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS) ffdl_dp_kernel(
       if (tid == 0) sc.meta[rr] = meta;
       continue;
     }
+    for (int i = tid; i < n; i += kThreads) a.out_gpus[o + i] = 0;  // :38-40
     if (n > a.max_jobs || K > a.max_total) {
       meta.st = VODA_ST_BOUND;
       if (tid == 0) sc.meta[rr] = meta;
@@ -372,65 +373,118 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS) ffdl_dp_kernel(
   }
 }
 
-// Kernel B: backtrack (:116-125) + deferred validateResult (:42).  One warp per round: the
-// chase through SOL is a chain of dependent loads, so thousands of rounds run it side by side.
+// Kernel B: backtrack (:116-125) + deferred validateResult (:42).
+// The chase through SOL is a chain of J dependent loads (row j-1 is read at k - g_j), so it is
+// all latency.  Each LANE chases one round (32 independent chains per warp, every round of the
+// batch in flight at once), eight rows at a time: the row constants (perm, klim) of the block
+// are loaded up front, and the SOL lines the NEXT block will touch are prefetched into L2 —
+// the position can only drift down by the g's chosen on the way, a few bytes per row — so the
+// dependent loads hit L2 instead of HBM.  Then the warp validates its 32 rounds one after the
+// other with coalesced reads.
 constexpr int kBtThreads = 128;
+constexpr int kBtBlock = 8;  // rows per chase block
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
 __global__ void __launch_bounds__(kBtThreads) ffdl_backtrack_kernel(AllocArgs a, int r0, int count, FfdlScratch sc,
                                                                     int K4cap) {
   const int lane = threadIdx.x & 31;
-  const int rr = blockIdx.x * (kBtThreads / 32) + (threadIdx.x >> 5);
-  if (rr >= count) return;
-  const int r = r0 + rr;
-  const int o = a.job_off[r] - a.job_base;
-  const int n = a.job_off[r + 1] - a.job_off[r];
-  const FfdlMeta meta = sc.meta[rr];
-  if (n == 0) {
-    if (lane == 0) a.out_status[r] = VODA_ST_OK;
-    return;
-  }
-  for (int i = lane; i < n; i += 32) a.out_gpus[o + i] = 0;  // :38-40
-  if (meta.st == VODA_ST_BOUND) {
-    if (lane == 0) a.out_status[r] = VODA_ST_BOUND;
-    return;
-  }
-  __syncwarp();
-  if (meta.st == VODA_ST_OK && lane == 0) {
-    const unsigned char* slab = sc.sol + (size_t)rr * sc.slabBytes;
-    const int32_t* gperm = sc.perm + (size_t)rr * sc.Jcap;
-    const int32_t* gklim = sc.klim + (size_t)rr * sc.Jcap;
-    const size_t stride = (size_t)K4cap * 4 * (size_t)meta.elem;
-    int k = meta.K;
-    for (int j = meta.J; j > 0; j--) {
-      int g = 0;  // SOL[j][0] == 0
-      const int kk = min(k, gklim[j - 1]);  // SOL[j][k] is constant from the row's saturation point on
-      if (kk > 0) {
-        const unsigned char* row = slab + (size_t)(j - 1) * stride;
-        g = meta.elem == 1 ? (int)row[kk - 1] : (int)reinterpret_cast<const uint16_t*>(row)[kk - 1];
+  const int rr0 = (blockIdx.x * (kBtThreads / 32) + (threadIdx.x >> 5)) * 32;
+  if (rr0 >= count) return;
+  // ---- phase 1: one chase per lane
+  {
+    const int rr = rr0 + lane;
+    if (rr < count) {
+      const int r = r0 + rr;
+      const int o = a.job_off[r] - a.job_base;
+      const FfdlMeta meta = sc.meta[rr];
+      if (meta.st == VODA_ST_OK && meta.J > 0) {
+        const unsigned char* slab = sc.sol + (size_t)rr * sc.slabBytes;
+        const int32_t* gperm = sc.perm + (size_t)rr * sc.Jcap;
+        const int32_t* gklim = sc.klim + (size_t)rr * sc.Jcap;
+        const size_t stride = (size_t)K4cap * 4 * (size_t)meta.elem;
+        const int es = meta.elem;  // bytes per SOL entry
+        int k = meta.K;
+        auto prefetch_rows = [&](int jtop) {  // rows jtop, jtop-1, ... (kBtBlock of them), around position k
+          for (int d = 0; d < kBtBlock && jtop - d > 0; d++) {
+            const int j = jtop - d;
+            const int kk = min(k, gklim[j - 1]);
+            if (kk > 0) {
+              const unsigned char* p = slab + (size_t)(j - 1) * stride + (size_t)(kk - 1) * es;
+              prefetch_l2(p);
+              if (kk * es > 96) prefetch_l2(p - 96);
+            }
+          }
+        };
+        prefetch_rows(meta.J);
+        for (int jb = meta.J; jb > 0; jb -= kBtBlock) {
+          int pj[kBtBlock], kl[kBtBlock];
+#pragma unroll
+          for (int d = 0; d < kBtBlock; d++) {
+            const int j = jb - d;
+            pj[d] = j > 0 ? gperm[j - 1] : 0;
+            kl[d] = j > 0 ? gklim[j - 1] : 0;
+          }
+          prefetch_rows(jb - kBtBlock);
+#pragma unroll
+          for (int d = 0; d < kBtBlock; d++) {
+            const int j = jb - d;
+            if (j <= 0) break;
+            int g = 0;  // SOL[j][0] == 0
+            const int kk = min(k, kl[d]);  // SOL[j][k] is constant from the row's saturation point on
+            if (kk > 0) {
+              const unsigned char* row = slab + (size_t)(j - 1) * stride;
+              g = es == 1 ? (int)row[kk - 1] : (int)reinterpret_cast<const uint16_t*>(row)[kk - 1];
+            }
+            a.out_gpus[o + pj[d]] = g;
+            k -= g;
+          }
+        }
       }
-      a.out_gpus[o + gperm[j - 1]] = g;
-      k -= g;
     }
   }
   __syncwarp();
-  // validateResult (utils.go:18-42); a panic it raises replaces the one in flight
-  int worst = 99;
-  long long sum = 0;
-  for (int i = lane; i < n; i += 32) {
-    const int v = a.out_gpus[o + i];
-    int st = 99;
-    if (v < 0) st = VODA_ST_NEGATIVE;
-    else if (v > 0 && v < a.min_proc[o + i]) st = VODA_ST_LESS_THAN_MIN;
-    else if (v > a.max_proc[o + i]) st = VODA_ST_EXCEEDED_MAX;
-    worst = min(worst, st);
-    sum += v;
-  }
-  for (int d = 16; d > 0; d >>= 1) {
-    worst = min(worst, __shfl_xor_sync(0xffffffffu, worst, d));
-    sum += __shfl_xor_sync(0xffffffffu, sum, d);
-  }
-  if (lane == 0) {
-    int v = worst != 99 ? worst : (sum > (long long)meta.K ? VODA_ST_EXCEEDED_TOTAL : VODA_ST_OK);
-    a.out_status[r] = v ? v : meta.st;
+  // ---- phase 2: validateResult (utils.go:18-42) per round; a panic it raises replaces the one in flight
+  for (int q = 0; q < 32 && rr0 + q < count; q++) {
+    const int rr = rr0 + q;
+    const int r = r0 + rr;
+    const int o = a.job_off[r] - a.job_base;
+    const int n = a.job_off[r + 1] - a.job_off[r];
+    const FfdlMeta meta = sc.meta[rr];
+    if (n == 0 || meta.st == VODA_ST_BOUND) {
+      if (lane == 0) a.out_status[r] = n == 0 ? VODA_ST_OK : VODA_ST_BOUND;
+      continue;
+    }
+    int worst = 99;
+    long long sum = 0;
+    for (int base = 0; base < n; base += 32 * 8) {  // 24 loads in flight per lane, then the checks
+      int v[8], mn[8], mx[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        const int i = base + 32 * u + lane;
+        const bool ok = i < n;
+        v[u] = ok ? a.out_gpus[o + i] : 0;
+        mn[u] = ok ? a.min_proc[o + i] : 0;
+        mx[u] = ok ? a.max_proc[o + i] : 0x7fffffff;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        int st = 99;
+        if (v[u] < 0) st = VODA_ST_NEGATIVE;
+        else if (v[u] > 0 && v[u] < mn[u]) st = VODA_ST_LESS_THAN_MIN;
+        else if (v[u] > mx[u]) st = VODA_ST_EXCEEDED_MAX;
+        worst = min(worst, st);
+        sum += v[u];
+      }
+    }
+    for (int d = 16; d > 0; d >>= 1) {
+      worst = min(worst, __shfl_xor_sync(0xffffffffu, worst, d));
+      sum += __shfl_xor_sync(0xffffffffu, sum, d);
+    }
+    if (lane == 0) {
+      int vv = worst != 99 ? worst : (sum > (long long)meta.K ? VODA_ST_EXCEEDED_TOTAL : VODA_ST_OK);
+      a.out_status[r] = vv ? vv : meta.st;
+    }
   }
 }
 
@@ -497,7 +551,7 @@ cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* sc
   ffdl_dp_kernel<<<grid, kThreads, smem, stream>>>(a, r0, count, sc, K4cap, SW, Jp);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  const int perBlock = kBtThreads / 32;
+  const int perBlock = (kBtThreads / 32) * 32;  // rounds per block: one lane per round
   ffdl_backtrack_kernel<<<(count + perBlock - 1) / perBlock, kBtThreads, 0, stream>>>(a, r0, count, sc, K4cap);
   return cudaGetLastError();
 }
