@@ -289,7 +289,6 @@ def main():
         def step_e2e():
             ctx.allocate(hbatch, h_out, h_st)
 
-        from vodascheduler_b200.batch import _ALLOC_ARRAYS
         h2d = in_bytes
         d2h = 4 * inputs.jobs + 4 * R
     elif wl["kind"] == "munkres":

@@ -316,7 +316,7 @@ int voda_allocate_dev(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* d_out_g
   if (rc) return rc;
   if (b->rounds == 0) return VODA_OK;
   if (!d_out_gpus || !d_out_status) return fail(ctx, VODA_E_INVALID, "null output");
-  if (b->max_jobs <= 0 || b->max_total_gpu < 0 || (b->max_total_gpu == 0 && false))
+  if (b->max_jobs <= 0 || b->max_total_gpu < 0)
     return fail(ctx, VODA_E_INVALID, "voda_allocate_dev needs max_jobs (and max_total_gpu) declared");
   CU(cudaSetDevice(ctx->device));
   AllocArgs a = make_args(b);
