@@ -117,6 +117,20 @@ __device__ inline void block_argsort_by(int* perm, int P, Less less) {
   }
 }
 
+// Rank sort for small rounds: perm[rank(i)] = i where rank(i) = #{j : less(j, i)}; `less` must be
+// a strict total order on [0, n).  One pass over the n keys per thread (they are read as
+// shared-memory broadcasts) and a single barrier, against log^2(n) barriers for the bitonic
+// network: cheaper up to n of about a hundred.  All threads of the CTA must call it.
+template <typename Less>
+__device__ inline void block_ranksort_by(int* perm, int n, Less less) {
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    int rank = 0;
+    for (int j = 0; j < n; j++) rank += less(j, i) ? 1 : 0;
+    perm[rank] = i;
+  }
+  __syncthreads();
+}
+
 __device__ inline void block_argsort(const int64_t* hi, const int32_t* lo, int* perm, int n, int P) {
   block_argsort_by(perm, P, [=](int a, int b) { return key_less(hi, lo, n, a, b); });
 }

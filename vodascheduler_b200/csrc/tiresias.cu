@@ -26,7 +26,8 @@
 namespace voda {
 namespace {
 
-constexpr int kThreads = 128;
+constexpr int kThreads = 128;     // upper bound; rounds of <= 64 jobs run with 64 threads
+constexpr int kRankSortMax = 96;  // rounds up to this size use the rank sort
 
 struct TirSmem {
   int64_t* khi;
@@ -86,6 +87,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     sm.table = reinterpret_cast<float*>(p);
   }
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nth = blockDim.x;
   const bool elastic = a.algo == VODA_ALGO_ELASTIC_TIRESIAS;
   const int Q = a.queue_num;
   const int W = a.stride;
@@ -95,7 +97,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     const int n = a.job_off[rd + 1] - a.job_off[rd];
     const int total = a.total_gpu[rd];
     if (n > a.max_jobs) {
-      for (int i = tid; i < n; i += kThreads) a.out_gpus[o + i] = 0;
+      for (int i = tid; i < n; i += nth) a.out_gpus[o + i] = 0;
       if (tid == 0) a.out_status[rd] = VODA_ST_BOUND;
       continue;
     }
@@ -103,9 +105,26 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     // stage the speedup table (coalesced) and the per-job scalars
     if (elastic && tableInSmem) {
       const float* src = a.speedup + (size_t)o * (size_t)W;
-      for (int x = tid; x < n * W; x += kThreads) sm.table[x] = src[x];
+      const int tot = n * W;
+      if (((reinterpret_cast<uintptr_t>(src) & 7) == 0) && (tot & 1) == 0) {
+        // 8-byte loads, four in flight per thread: the staging loop is pure latency otherwise
+        const float2* s2 = reinterpret_cast<const float2*>(src);
+        float2* d2 = reinterpret_cast<float2*>(sm.table);
+        const int m = tot >> 1;
+        for (int x = tid; x < m; x += 4 * nth) {
+          float2 v[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++)
+            if (x + u * nth < m) v[u] = s2[x + u * nth];
+#pragma unroll
+          for (int u = 0; u < 4; u++)
+            if (x + u * nth < m) d2[x + u * nth] = v[u];
+        }
+      } else {
+        for (int x = tid; x < tot; x += nth) sm.table[x] = src[x];
+      }
     }
-    for (int i = tid; i < n; i += kThreads) {
+    for (int i = tid; i < n; i += nth) {
       const int pr = a.priority[o + i];
       sm.prio[i] = pr;
       sm.kq[i] = (pr >= 0 && pr < Q) ? pr : Q;
@@ -126,23 +145,27 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
       return tableInSmem ? sm.table[i * W + g] : a.speedup[(size_t)(o + i) * (size_t)W + (size_t)g];
     };
     if (elastic)
-      for (int i = tid; i < n; i += kThreads) sm.gain[i] = S(i, sm.mn[i]) / (float)sm.mn[i];  // :58
+      for (int i = tid; i < n; i += nth) sm.gain[i] = S(i, sm.mn[i]) / (float)sm.mn[i];  // :58
     // 2. queues
     {
       const int64_t* khi = sm.khi;
       const int32_t* klo = sm.klo;
       const int32_t* kq = sm.kq;
-      block_argsort_by(sm.perm, next_pow2(n > 0 ? n : 1), [=](int x, int y) {
+      auto less = [=](int x, int y) {
         if (y >= n) return x < n ? true : x < y;
         if (x >= n) return false;
         if (kq[x] != kq[y]) return kq[x] < kq[y];
         if (khi[x] != khi[y]) return khi[x] < khi[y];
         if (klo[x] != klo[y]) return klo[x] < klo[y];
         return x < y;
-      });
+      };
+      if (n <= kRankSortMax)
+        block_ranksort_by(sm.perm, n, less);
+      else
+        block_argsort_by(sm.perm, next_pow2(n > 0 ? n : 1), less);
     }
     int inq = 0;
-    for (int t = tid; t < n; t += kThreads) {
+    for (int t = tid; t < n; t += nth) {
       const int i = sm.perm[t];
       sm.need[t] = a.num_proc[o + i];
       inq += sm.kq[i] < Q;
@@ -159,7 +182,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     __syncthreads();
     long long free = sm.red[2];
     int accepted = 0;
-    for (int t = tid; t < nq; t += kThreads) {
+    for (int t = tid; t < nq; t += nth) {
       if (sm.acc[t]) {
         const int i = sm.perm[t];
         const int np = sm.need[t];
@@ -173,7 +196,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     __syncthreads();
     if (!elastic) {
       // Tiresias: only jobs inside a queue are in the result map (tiresias.go:81-90)
-      for (int i = tid; i < n; i += kThreads) {
+      for (int i = tid; i < n; i += nth) {
         a.out_gpus[o + i] = sm.r[i];
         sm.live[i] = sm.kq[i] >= Q;  // "skip" flag for validateResult
       }
@@ -186,7 +209,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     // 4. compaction (:89-102)
     if (pendings > a.compaction) {
       long long freed = 0;
-      for (int i = tid; i < n; i += kThreads) {
+      for (int i = tid; i < n; i += nth) {
         const int q = sm.kq[i];
         if (q >= 1 && q < Q && sm.r[i] != 0) {
           freed += sm.r[i] - sm.mn[i];
@@ -203,7 +226,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     }
     // 5. prune (:107-115); free is frozen here
     int nl = 0;
-    for (int i = tid; i < n; i += kThreads) {
+    for (int i = tid; i < n; i += nth) {
       const bool lv = !(sm.r[i] >= sm.mx[i] || free < (long long)sm.mn[i]);
       sm.live[i] = lv;
       sm.stamp[i] = -i;
@@ -273,7 +296,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
       }
     }
     __syncthreads();
-    for (int i = tid; i < n; i += kThreads) a.out_gpus[o + i] = sm.r[i];
+    for (int i = tid; i < n; i += nth) a.out_gpus[o + i] = sm.r[i];
     __syncthreads();
     const int v = block_validate(a, o, n, total, a.out_gpus + o, nullptr, sm.red);
     if (tid == 0) a.out_status[rd] = v;
@@ -302,12 +325,13 @@ cudaError_t launch_tiresias(const AllocArgs& a, int sms, cudaStream_t stream) {
     if (e != cudaSuccess) return e;
   }
   int perSm = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, tiresias_kernel, kThreads, smem);
+  const int threads = a.max_jobs <= 64 ? 64 : kThreads;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, tiresias_kernel, threads, smem);
   if (e != cudaSuccess) return e;
   if (perSm < 1) perSm = 1;
   int grid = sms * perSm;
   if (a.rounds < grid) grid = a.rounds;
-  tiresias_kernel<<<grid, kThreads, smem, stream>>>(a, Jp, in ? 1 : 0);
+  tiresias_kernel<<<grid, threads, smem, stream>>>(a, Jp, in ? 1 : 0);
   return cudaGetLastError();
 }
 
