@@ -34,6 +34,7 @@ struct TirSmem {
   long long* red;  // [4]
   int32_t* klo;
   int32_t* kq;     // queue index (Q for "no queue")
+  int4* key4;      // [kRankSortMax] {queue, nsec, sec lo, sec hi}: one broadcast LDS.128 per compare
   int* perm;
   int32_t* r;
   float* gain;
@@ -68,6 +69,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
   TirSmem sm;
   {
     unsigned char* p = smem_raw;
+    sm.key4 = reinterpret_cast<int4*>(p); p += 16 * kRankSortMax;
     sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Jp;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
     sm.klo = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
@@ -130,6 +132,8 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
       sm.kq[i] = (pr >= 0 && pr < Q) ? pr : Q;
       sm.khi[i] = a.first_sec[o + i];
       sm.klo[i] = a.first_nsec ? a.first_nsec[o + i] : 0;
+      if (n <= kRankSortMax)
+        sm.key4[i] = make_int4(sm.kq[i], sm.klo[i], (int)(uint32_t)(uint64_t)sm.khi[i], (int)(sm.khi[i] >> 32));
       sm.mn[i] = a.min_proc[o + i];
       sm.mx[i] = a.max_proc[o + i];
       sm.r[i] = 0;
@@ -159,8 +163,27 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
         if (klo[x] != klo[y]) return klo[x] < klo[y];
         return x < y;
       };
-      if (n <= kRankSortMax)
-        block_ranksort_by(sm.perm, n, less);
+      if (n <= kRankSortMax) {
+        // rank sort on the packed records: rank(i) = #{j : key_j < key_i or (== and j < i)}
+        for (int i = tid; i < n; i += nth) {
+          const int4 ki = sm.key4[i];
+          const long long si = ((long long)ki.w << 32) | (unsigned)ki.z;
+          int rank = 0;
+#pragma unroll 4
+          for (int j = 0; j < n; j++) {
+            const int4 kj = sm.key4[j];
+            const long long sj = ((long long)kj.w << 32) | (unsigned)kj.z;
+            bool lt;
+            if (kj.x != ki.x) lt = kj.x < ki.x;
+            else if (sj != si) lt = sj < si;
+            else if (kj.y != ki.y) lt = kj.y < ki.y;
+            else lt = j < i;
+            rank += lt ? 1 : 0;
+          }
+          sm.perm[rank] = i;
+        }
+        __syncthreads();
+      }
       else
         block_argsort_by(sm.perm, next_pow2(n > 0 ? n : 1), less);
     }
@@ -303,7 +326,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
   }
 }
 
-size_t tir_fixed_smem(int Jp) { return (size_t)Jp * (8 + 4 * 10 + 2) + 8 * 4 + 4 * 8 + 32; }
+size_t tir_fixed_smem(int Jp) { return (size_t)Jp * (8 + 4 * 10 + 2) + 16 * kRankSortMax + 8 * 4 + 4 * 8 + 32; }
 
 }  // namespace
 
