@@ -35,6 +35,7 @@ namespace voda {
 namespace {
 
 constexpr int kThreads = 128;
+constexpr int kWarps = kThreads / 32;
 constexpr unsigned short kDead = 0xFFFF;
 
 struct AfslSmem {
@@ -51,6 +52,8 @@ struct AfslSmem {
   unsigned short* perm;        // sr -> job index within the round
   float* lenT;                 // [CH][Jp]: len(sr, w), w = 1..CH
   long long* red;              // [4]
+  int* sbeat;                  // [2][kWarps] first beating position per warp (double-buffered) + 1
+  float* schamp;               // [6] state of a job that just became the champion
   // sort scratch, aliased over rem/L/Rr/r (16 bytes per job)
   int64_t* khi;
   int32_t* klo;
@@ -63,6 +66,8 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
   {
     unsigned char* p = smem_raw;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
+    sm.sbeat = reinterpret_cast<int*>(p); p += 4 * (2 * kWarps + 2);
+    sm.schamp = reinterpret_cast<float*>(p); p += 4 * 8;
     sm.khi = reinterpret_cast<int64_t*>(p);
     sm.klo = reinterpret_cast<int32_t*>(p + 8 * (size_t)Jp);
     sm.perm32 = reinterpret_cast<int*>(p + 12 * (size_t)Jp);
@@ -125,7 +130,7 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
     }
     __syncthreads();
 
-    if (warp == 0) {
+    {
       // len(x, w): hot columns from shared memory, the rest divided on the fly (w >= W is a
       // map miss: rem / 0)
       auto LEN = [&](int x, int w) -> float {
@@ -133,6 +138,8 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
         if (w <= CH) return sm.lenT[(size_t)(w - 1) * Jp + x];
         return sm.rem[x] / S(sm.perm[x], w);
       };
+      // Every thread of the CTA carries the same scalar state (computed from the same shared
+      // memory values), so the control flow below is uniform across the CTA.
       int len = n;        // entries in order[] (live + dead)
       int dead = 0;
       int head = 0;       // first live position
@@ -141,6 +148,7 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
       int champPos = -1;  // ... and where it sits
       long long free = total;
       int nlive = n;
+      int parity = 0;
       while (free > 0 && nlive > 0) {  // :47
         // ---- topPriority: fold from startPos ------------------------------------------
         if (champ < 0) {
@@ -149,70 +157,82 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
           champPos = head;
           startPos = head + 1;
         }
-        // champion state, uniform across the warp
+        // champion state, uniform across the CTA
         int c = champ, cp = champPos;
         int rc = sm.r[c];
         float remc = sm.rem[c], Lc = sm.L[c], Rc = sm.Rr[c];
         float lenA = sm.self[c];
-        for (int base = startPos & ~31; base < len; base += 32) {
-          const int p = base + lane;
-          const int jb = (p < len && p >= startPos) ? (int)sm.order[p] : (int)kDead;
-          bool pend = jb != kDead;
-          // challenger-side values (independent of the champion)
+        // SPECULATION ACROSS WARPS: the kThreads positions from `pos` on are all tested against
+        // the champion entering `pos`.  On this workload the champion changes about once per
+        // pick while a fold is ~10 chunks of 32 long, so most groups pass without a change and
+        // the fold advances kThreads positions per step; when some position does beat the
+        // champion, everything before it is final, that job becomes the champion and the
+        // fold resumes right behind it — exactly the left fold, evaluated in wider steps.
+        int pos = startPos;
+        while (pos < len) {
+          const int p = pos + tid;
+          const int jb = p < len ? (int)sm.order[p] : (int)kDead;
+          const bool pend = jb != kDead;
           int rj = 0;
           float remj = 0.f, Lj = 0.f, Rj = 0.f;
+          bool beat = false;
           if (pend) {
             rj = sm.r[jb];
             remj = sm.rem[jb];
             Lj = sm.L[jb];
             Rj = sm.Rr[jb];
-          }
-          while (true) {
-            bool beat = false;
-            if (pend) {
-              if (rc == 0 && rj == 0) {
-                beat = remc >= remj;  // :77-79 later job wins ties
+            if (rc == 0 && rj == 0) {
+              beat = remc >= remj;  // :77-79 later job wins ties
+            } else {
+              const float lenB = LEN(jb, rc);  // champion's count for both (:82)
+              if (lenA >= lenB) {
+                // swap: short = challenger, long = champion; champion survives iff left > right
+                beat = !(Lc > Rj);
               } else {
-                const float lenB = LEN(jb, rc);  // champion's count for both (:82)
-                if (lenA >= lenB) {
-                  // swap: short = challenger, long = champion; champion survives iff left > right
-                  beat = !(Lc > Rj);
-                } else {
-                  beat = Lj > Rc;  // short = champion, long = challenger
-                }
+                beat = Lj > Rc;  // short = champion, long = challenger
               }
             }
-            const unsigned m = __ballot_sync(full, beat);
-            if (!m) {
-              if (pend) {
-                sm.champIn[p] = (unsigned short)c;
-                sm.champInPos[p] = (unsigned short)cp;
-              }
-              break;
-            }
-            const int f = __ffs(m) - 1;
-            if (pend && lane <= f) {
-              sm.champIn[p] = (unsigned short)c;
-              sm.champInPos[p] = (unsigned short)cp;
-              pend = false;
-            }
-            // lane f becomes the champion: its whole state comes over by shuffle
-            c = __shfl_sync(full, jb, f);
-            cp = base + f;
-            rc = __shfl_sync(full, rj, f);
-            remc = __shfl_sync(full, remj, f);
-            Lc = __shfl_sync(full, Lj, f);
-            Rc = __shfl_sync(full, Rj, f);
-            lenA = sm.self[c];  // uniform broadcast read
           }
+          const unsigned m = __ballot_sync(full, beat);
+          if (lane == 0) sm.sbeat[parity * kWarps + warp] = m ? pos + 32 * warp + __ffs(m) - 1 : 0x7fffffff;
+          __syncthreads();
+          int first = 0x7fffffff;
+#pragma unroll
+          for (int w = 0; w < kWarps; w++) first = min(first, sm.sbeat[parity * kWarps + w]);
+          parity ^= 1;
+          if (pend && p <= first) {  // the champion entering these positions is final
+            sm.champIn[p] = (unsigned short)c;
+            sm.champInPos[p] = (unsigned short)cp;
+          }
+          if (first == 0x7fffffff) {
+            pos += kThreads;
+            continue;
+          }
+          if (p == first) {  // this job takes over: publish its state
+            sm.schamp[0] = __int_as_float(jb);
+            sm.schamp[1] = __int_as_float(rj);
+            sm.schamp[2] = remj;
+            sm.schamp[3] = Lj;
+            sm.schamp[4] = Rj;
+            sm.schamp[5] = sm.self[jb];
+          }
+          __syncthreads();
+          c = __float_as_int(sm.schamp[0]);
+          cp = first;
+          rc = __float_as_int(sm.schamp[1]);
+          remc = sm.schamp[2];
+          Lc = sm.schamp[3];
+          Rc = sm.schamp[4];
+          lenA = sm.schamp[5];
+          pos = first + 1;
         }
         // ---- give it one GPU (:49-57) ----------------------------------------------------
         const int w = c, wpos = cp;
-        __syncwarp();
         const int nr = rc + 1;
         free -= 1;
         const bool removed = nr >= sm.mx[w];
-        if (lane == 0) {
+        __syncthreads();  // champIn of this fold is complete; everyone has read the old state of w
+        if (tid == 0) {
           sm.r[w] = nr;
           const int job = sm.perm[w];
           const float s0 = S(job, nr), s1 = S(job, nr + 1);
@@ -235,24 +255,29 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
           champPos = sm.champInPos[wpos];
           startPos = removed ? wpos + 1 : wpos;
         }
-        __syncwarp();
-        // ---- compaction of the live list ---------------------------------------------------
+        __syncthreads();
+        // ---- compaction of the live list (warp 0; the condition is uniform) -----------------
         if (dead >= 64 || (dead > 0 && dead * 4 >= len)) {
-          int outp = 0;
-          for (int base = 0; base < len; base += 32) {
-            const int p = base + lane;
-            const int v = p < len ? (int)sm.order[p] : (int)kDead;
-            const unsigned keep = __ballot_sync(full, v != kDead);
-            const int dst = outp + __popc(keep & ((1u << lane) - 1u));
-            __syncwarp();
-            if (v != kDead) sm.order[dst] = (unsigned short)v;
-            outp += __popc(keep);
-            __syncwarp();
+          if (warp == 0) {
+            int outp = 0;
+            for (int base = 0; base < len; base += 32) {
+              const int p = base + lane;
+              const int v = p < len ? (int)sm.order[p] : (int)kDead;
+              const unsigned keep = __ballot_sync(full, v != kDead);
+              const int dst = outp + __popc(keep & ((1u << lane) - 1u));
+              __syncwarp();
+              if (v != kDead) sm.order[dst] = (unsigned short)v;
+              outp += __popc(keep);
+              __syncwarp();
+            }
+            if (lane == 0) sm.sbeat[2 * kWarps] = outp;
           }
-          len = outp;
+          __syncthreads();
+          len = sm.sbeat[2 * kWarps];
           dead = 0;
           head = 0;
           champ = -1;  // positions moved: cached champions are void
+          __syncthreads();
         }
       }
     }
@@ -265,7 +290,7 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
 }
 
 // shared memory: 32 bytes per job + the hot len() columns
-size_t afsl_fixed_smem(int Jp) { return (size_t)Jp * 32 + 8 * 4 + 32; }
+size_t afsl_fixed_smem(int Jp) { return (size_t)Jp * 32 + 8 * 4 + 4 * (2 * kWarps + 2) + 4 * 8 + 32; }
 
 int afsl_hot_columns(const AllocArgs& a, int Jp) {
   // as many columns as still leave room for 4 CTAs per SM (about 55 KB each), at most W - 1
