@@ -51,6 +51,7 @@ struct FfdlSmem {
   int* perm;         // [Jp]
   int32_t* smax;     // [Jp]  max_proc in sorted order
   int32_t* scum;     // [Jp]  min(K, sum of clamp(max_proc, 0, K) over the first j+1 sorted jobs)
+  int32_t* slo;      // [Jp]  max(0, K - sum of clamp(max_proc, 0, K) over the sorted jobs after j)
   float* srmax;      // [Jp]  max over the row's usable g of S_j[g] (-inf if none)
   long long* red;    // [2]
   int* misc;         // [4]
@@ -226,7 +227,15 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, 
     // c_j = max(-10000, max_g (S_j[g] + c_{j-1})) = max(-10000, (max_g S_j[g]) + c_{j-1}): rounding
     // is monotone, so the maximum commutes with the addition exactly
     const float ccur = fmaxf(-10000.0f, sm.srmax[j - 1] + cprev);
+    // The other side of the budget: the backtrack starts at k = K and gives up at most max_i
+    // per row, so row j is only ever consulted at k >= K - (sum of the later jobs' max sizes),
+    // or at its saturation point klim_j when that is lower; klo_j is the smaller of the two,
+    // and a cell at k >= klo_j reads row j-1 at k-g >= klo_j - max_j >= klo_{j-1}.  Tiles
+    // wholly below klo_j feed neither P[J][K] nor any SOL entry the backtrack can read: they
+    // are not computed (what the row buffer holds there is never read by a cell that matters).
+    const int klo = sm.slo[j - 1];
     for (int tq = tid; tq < KT; tq += kThreads) {
+      if (kCells * tq + kCells < klo) continue;
       if (kCells * tq + 1 > klim) {
         const float4 c4 = make_float4(ccur, ccur, ccur, ccur);
 #pragma unroll
@@ -288,6 +297,7 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS) ffdl_dp_kernel(
     sm.perm = reinterpret_cast<int*>(p); p += sizeof(int) * (size_t)Jp;
     sm.smax = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
     sm.scum = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
+    sm.slo = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
     sm.srmax = reinterpret_cast<float*>(p); p += sizeof(float) * (size_t)Jp;
     sm.misc = reinterpret_cast<int*>(p);
   }
@@ -351,6 +361,13 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS) ffdl_dp_kernel(
         const int kl = (int)min(acc, (long long)K);
         sm.scum[j] = kl;
         gklim[j] = kl;
+      }
+      acc = 0;
+      for (int j = J - 1; j >= 0; j--) {
+        // (the backtrack reads SOL[j] at min(k, klim_j), so the saturation point itself must
+        // stay inside the computed band when it lies below the cone)
+        sm.slo[j] = min((int)max(0LL, (long long)K - acc), sm.scum[j]);
+        acc += max(0, min(sm.smax[j], K));
       }
     }
     __syncthreads();
@@ -498,7 +515,7 @@ static void ffdl_shape(const AllocArgs& a, int* K4cap, int* SW, int* Jp, size_t*
   *SW = (sw + 3) & ~3;
   *Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
   *smem = sizeof(float4) * 2 * (size_t)(*K4cap + 1) + sizeof(float) * 2 * (size_t)(*SW) +
-          (sizeof(int64_t) + 5 * sizeof(int32_t)) * (size_t)(*Jp) + 2 * sizeof(long long) + 4 * sizeof(int);
+          (sizeof(int64_t) + 6 * sizeof(int32_t)) * (size_t)(*Jp) + 2 * sizeof(long long) + 4 * sizeof(int);
 }
 
 static size_t ffdl_jcap(const AllocArgs& a) {
