@@ -150,9 +150,9 @@ int dispatch_alloc(voda_ctx* ctx, const AllocArgs& a, DevBuf& scratch, cudaStrea
       if (ffdl_smem_bytes(a) > 200 * 1024)
         return fail(ctx, VODA_E_UNSUPPORTED, "FfDL: total_gpu / jobs too large for one CTA's shared memory");
       // every round keeps its SOL slab until the backtrack kernel has read it: cap the scratch
-      // at 8 GiB and walk larger batches in sub-batches (two launches each)
+      // at 16 GiB and walk larger batches in sub-batches (two launches each)
       const size_t per = (ffdl_scratch_per_round(a) + 255) & ~(size_t)255;
-      const size_t budget = (size_t)8 << 30;
+      const size_t budget = (size_t)16 << 30;
       int sub = (int)std::min<size_t>((size_t)a.rounds, std::max<size_t>(1, budget / per));
       int rc = ensure(ctx, scratch, per * (size_t)sub, stream);
       if (rc) return rc;
