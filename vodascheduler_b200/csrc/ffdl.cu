@@ -44,31 +44,33 @@ namespace {
 #ifndef VODA_FFDL_THREADS
 #define VODA_FFDL_THREADS 64
 #endif
-#ifndef VODA_FFDL_CELLS
-#define VODA_FFDL_CELLS 8
-#endif
 #ifndef VODA_FFDL_MINBLOCKS
 #define VODA_FFDL_MINBLOCKS 12
 #endif
 constexpr int kThreads = VODA_FFDL_THREADS;
-constexpr int kCells = VODA_FFDL_CELLS;  // adjacent cells per thread
-constexpr int kGroups = kCells / 4 + 1;  // float4 groups of row j-1 in the sliding window
-static_assert(kCells % 4 == 0, "cells per thread come in float4 groups");
+constexpr int kCells = 8;  // adjacent cells per thread: two float4 groups, a three-group window
 
+// Per-row constants, worked out once per round after the sort and read back with one LDS.64
+// and one LDS.32 per row: four 16-bit fields packed in a word, and the row maximum.
+//   bits  0..15  nblk   blocks of 4 g-steps served from the table; bit 15: the row also has candidates g >= W
+//   bits 16..31  tc0    tiles tc0 .. tcE-1 are computed
+//   bits 32..47  tcE
+//   bits 48..63  fillE  tiles tcE .. fillE-1 are filled with the saturated constant
+__device__ __forceinline__ unsigned long long pack_row(int nblk, bool slow, int tc0, int tcE, int fillE) {
+  return (unsigned long long)(unsigned)(nblk | (slow ? 0x8000 : 0)) | ((unsigned long long)(unsigned)tc0 << 16) |
+         ((unsigned long long)(unsigned)tcE << 32) | ((unsigned long long)(unsigned)fillE << 48);
+}
+
+// Shared memory per CTA: two row buffers and 20 bytes per job; the sort keys' space is reused
+// for the row constants once the sort is done.
 struct FfdlSmem {
-  float4* rowA;      // [G4]  row buffers, group q = P[4q-3 .. 4q]
-  float4* rowB;      // [G4]
-  float* srow0;      // [SW]  S_j[1..] of even rows, -inf beyond the row's g limit
-  float* srow1;      // [SW]  ... of odd rows
-  int64_t* khi;      // [Jp]
-  int32_t* klo;      // [Jp]
-  int* perm;         // [Jp]
-  int32_t* smax;     // [Jp]  max_proc in sorted order
-  int32_t* scum;     // [Jp]  klim: min(K, sum of clamp(max_proc, 0, K) over the first j+1 sorted jobs)
-  int32_t* slo;      // [Jp]  cone: max(0, K - sum of clamp(max_proc, 0, K) over the sorted jobs after j)
-  float* srmax;      // [Jp]  max over the row's usable g of S_j[g] (-inf if none)
-  long long* red;    // [2]
-  int* misc;         // [4]
+  float4* rowA;    // [pad + G4]  row buffers, group q = P[4q-3 .. 4q], -inf groups in front
+  float4* rowB;    // [pad + G4]
+  int64_t* khi;    // [Jp]  sort key (seconds); after the sort: the packed row constants
+  int32_t* klo;    // [Jp]  sort key (nanoseconds); after the sort: srmax, max over the row's usable g of S_j[g]
+  int* perm;       // [Jp]  sorted position -> job; then smaxc = clamp(max_proc, 0, K) in sorted order
+  int32_t* pre;    // [Jp]  inclusive prefix sums of smaxc
+  float4* sring;   // [4][SW/4]  S rows of the current and the next rows
 };
 
 // What the DP kernel leaves per round for the backtrack kernel ...
@@ -97,11 +99,11 @@ struct FfdlScratch {
   int SW;
 };
 
-// Row buffers carry kPadGroups(SW) groups of -inf in front of group 0, so the window can slide
+// Row buffers carry pad_groups(SW) groups of -inf in front of group 0, so the window can slide
 // left of the row (k-g < 0) without a branch.
 __host__ __device__ constexpr int pad_groups(int SW) { return SW / 4 + 1; }
 
-// 4 g-steps (g = 4m+1 .. 4m+4) for the kCells cells of a tile: cell c at step s reads element
+// 4 g-steps (g = 4m+1 .. 4m+4) for the 8 cells of a tile: cell c at step s reads element
 // 3+c-s of the window (lo, mid, hi) = 12 consecutive floats of row j-1; two candidates per
 // three-input maximum.
 __device__ __forceinline__ void ffdl_block8(float (&best)[8], const float4 sq, const float4 lo, const float4 mid,
@@ -114,76 +116,68 @@ __device__ __forceinline__ void ffdl_block8(float (&best)[8], const float4 sq, c
   }
 }
 
-// One DP row for column tile `tq` (cells k = kCells*tq+1 .. kCells*tq+kCells).
+__device__ __forceinline__ void ffdl_store_tile(float4* __restrict__ cur, int qtop, const float (&best)[8]) {
+  cur[qtop + 1] = make_float4(best[0], best[1], best[2], best[3]);
+  cur[qtop + 2] = make_float4(best[4], best[5], best[6], best[7]);
+}
+
+// One DP row for column tile `tq` (cells k = 8*tq+1 .. 8*tq+8) when every candidate comes from
+// the first NB blocks of the table (g <= 4*NB): the common shapes, fully unrolled, S in registers.
 // Row storage: group q = P[4q-3 .. 4q].  For the block of g = 4m+1 .. 4m+4 the cells need
-// P[base-3 .. base+kCells-1], base = kCells*tq - 4m, i.e. groups q0 .. q0+kCells/4 with
-// q0 = (kCells/4)*tq - m; the next block slides the window down by one group (one LDS.128).
-__device__ __forceinline__ void ffdl_row_tile(const float4* __restrict__ prev, float4* __restrict__ cur,
-                                              const float* __restrict__ srow, int tq, int nblk, int gslow0,
-                                              int gslow1) {
-  float best[kCells];
+// P[base-3 .. base+8], base = 8*tq - 4m, i.e. groups q0 .. q0+2 with q0 = 2*tq - m.
+template <int NB>
+__device__ __forceinline__ void ffdl_tile_nb(const float4* __restrict__ prev, float4* __restrict__ cur, int tq,
+                                             const float4 sA, const float4 sB) {
+  float best[8];
 #pragma unroll
-  for (int c = 0; c < kCells; c++) best[c] = -10000.0f;
-  const int qtop = (kCells / 4) * tq;
-  const float4* s4 = reinterpret_cast<const float4*>(srow);
-  if constexpr (kCells == 8) {
-    // the window is three groups; instead of shifting registers after every block the three
-    // roles rotate through three unrolled copies of the block
-    float4 g0 = prev[qtop], g1 = prev[qtop + 1], g2 = prev[qtop + 2];
-    int m = 0;
-    for (; m + 3 <= nblk; m += 3) {
-      ffdl_block8(best, s4[m], g0, g1, g2);
+  for (int c = 0; c < 8; c++) best[c] = -10000.0f;
+  const int qtop = 2 * tq;
+  const float4 g0 = prev[qtop], g1 = prev[qtop + 1], g2 = prev[qtop + 2];
+  ffdl_block8(best, sA, g0, g1, g2);
+  if (NB >= 2) {
+    const float4 gm = prev[qtop - 1];
+    ffdl_block8(best, sB, gm, g0, g1);
+  }
+  ffdl_store_tile(cur, qtop, best);
+}
+
+// The general tile: any number of blocks (S read from the round's sorted S rows in global
+// memory), then the candidates g in [gslow0, gslow1] the dense table does not hold (the Go map
+// misses, S = 0; rare: max_j >= W).
+__device__ __forceinline__ void ffdl_tile_any(const float4* __restrict__ prev, float4* __restrict__ cur, int tq,
+                                              const float4* __restrict__ s4, int nblk, int gslow0, int gslow1) {
+  float best[8];
+#pragma unroll
+  for (int c = 0; c < 8; c++) best[c] = -10000.0f;
+  const int qtop = 2 * tq;
+  // the window is three groups; instead of shifting registers after every block the three
+  // roles rotate through three unrolled copies of the block
+  float4 g0 = prev[qtop], g1 = prev[qtop + 1], g2 = prev[qtop + 2];
+  int m = 0;
+  for (; m + 3 <= nblk; m += 3) {
+    ffdl_block8(best, s4[m], g0, g1, g2);
+    g2 = prev[qtop - m - 1];
+    ffdl_block8(best, s4[m + 1], g2, g0, g1);
+    g1 = prev[qtop - m - 2];
+    ffdl_block8(best, s4[m + 2], g1, g2, g0);
+    g0 = prev[qtop - m - 3];
+  }
+  if (m < nblk) {
+    ffdl_block8(best, s4[m], g0, g1, g2);
+    if (m + 1 < nblk) {
       g2 = prev[qtop - m - 1];
       ffdl_block8(best, s4[m + 1], g2, g0, g1);
-      g1 = prev[qtop - m - 2];
-      ffdl_block8(best, s4[m + 2], g1, g2, g0);
-      g0 = prev[qtop - m - 3];
-    }
-    if (m < nblk) {
-      ffdl_block8(best, s4[m], g0, g1, g2);
-      if (m + 1 < nblk) {
-        g2 = prev[qtop - m - 1];
-        ffdl_block8(best, s4[m + 1], g2, g0, g1);
-      }
-    }
-  } else {
-    float4 grp[kGroups];
-#pragma unroll
-    for (int i = 0; i < kGroups; i++) grp[i] = prev[qtop + i];
-    for (int m = 0; m < nblk; m++) {
-      float v[4 * kGroups];
-#pragma unroll
-      for (int i = 0; i < kGroups; i++) {
-        v[4 * i + 0] = grp[i].x;
-        v[4 * i + 1] = grp[i].y;
-        v[4 * i + 2] = grp[i].z;
-        v[4 * i + 3] = grp[i].w;
-      }
-      const float4 sq = s4[m];
-#pragma unroll
-      for (int c = 0; c < kCells; c++) {
-        best[c] = fmaxf(fmaxf(best[c], sq.x + v[3 + c]), sq.y + v[2 + c]);
-        best[c] = fmaxf(fmaxf(best[c], sq.z + v[1 + c]), sq.w + v[c]);
-      }
-#pragma unroll
-      for (int i = kGroups - 1; i > 0; i--) grp[i] = grp[i - 1];
-      grp[0] = prev[qtop - m - 1];
     }
   }
-  // g beyond the dense speedup table: the Go map misses, S = 0 (rare: max_j >= W)
   if (gslow1 >= gslow0) {
     const float* pf = reinterpret_cast<const float*>(prev);
 #pragma unroll
-    for (int c = 0; c < kCells; c++) {
-      const int k = kCells * tq + 1 + c;
+    for (int c = 0; c < 8; c++) {
+      const int k = 8 * tq + 1 + c;
       for (int g = gslow0; g <= gslow1 && g <= k; g++) best[c] = fmaxf(best[c], 0.0f + pf[k - g + 3]);
     }
   }
-#pragma unroll
-  for (int i = 0; i < kCells / 4; i++) {
-    const float4 b4 = make_float4(best[4 * i], best[4 * i + 1], best[4 * i + 2], best[4 * i + 3]);
-    cur[qtop + 1 + i] = b4;
-  }
+  ffdl_store_tile(cur, qtop, best);
 }
 
 // Bulk asynchronous copy shared -> global (cp.async.bulk, the TMA engine without a tensor map).
@@ -195,103 +189,165 @@ __device__ __forceinline__ void bulk_store(float* dst, const float4* src, uint32
 }
 __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+// 16-byte asynchronous copy global -> shared (LDGSTS)
+__device__ __forceinline__ void cp_async16(float4* dst, const float4* src) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Everything the row loop and the backtrack need to know about the rows of one round, worked
+// out once after the sort: the sorted S rows (to scratch), the row maxima, the two running
+// sums behind the trims, the tile ranges.
+__device__ void ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, int K, int KT, int SW,
+                                float* gs, FfdlRow* grows) {
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int W = a.stride;
+  unsigned long long* rowq = reinterpret_cast<unsigned long long*>(sm.khi);  // the sort keys are dead
+  float* srmax = reinterpret_cast<float*>(sm.klo);
+  int32_t* smaxc = sm.perm;  // slot j is read (perm) and then written (smaxc) by the same thread
+  int32_t* pre = sm.pre;
+  // a. a thread per row.  First the row's size limit (one dependent load per row, all rows of
+  //    the thread in flight together), then S_j[1..] with -inf beyond the row's table limit:
+  //    only the entries the row can use are read.
+#pragma unroll 4
+  for (int j = tid; j < J; j += kThreads) {
+    const int pj = sm.perm[j];
+    const int gmax = min(a.max_proc[o + pj], K);
+    smaxc[j] = max(0, gmax);
+    grows[j].job = pj;
+    grows[j].gmax = gmax;
+  }
+  for (int j = tid; j < J; j += kThreads) {
+    const int pj = grows[j].job;  // this thread's own stores
+    const int gmax = grows[j].gmax;
+    const int gt = min(gmax, W - 1);      // last g served from the table
+    const bool slow = gmax >= max(W, 1);  // candidates the table does not hold read S = 0 (a Go map miss)
+    const float* sj = a.speedup + (a.sp_off ? (size_t)a.sp_off[o + pj] : (size_t)(o + pj) * (size_t)W);
+    float4* gj = reinterpret_cast<float4*>(gs + (size_t)j * SW);
+    float rm = slow ? 0.0f : VODA_NEG_INF;
+#pragma unroll 3
+    for (int m = 0; m < SW / 4; m++) {
+      float v[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int g = 4 * m + u + 1;
+        v[u] = g <= gt ? sj[g] : VODA_NEG_INF;
+        rm = fmaxf(rm, v[u]);
+      }
+      gj[m] = make_float4(v[0], v[1], v[2], v[3]);
+    }
+    srmax[j] = rm;
+  }
+  __syncthreads();
+  // b. inclusive prefix sums of the usable sizes (warp 0, a contiguous chunk per lane)
+  if (warp == 0) {
+    const int per = (J + 31) / 32;
+    const int lo = min(lane * per, J), hi = min(lo + per, J);
+    int s = 0;
+    for (int i = lo; i < hi; i++) s += smaxc[i];
+    int incl = s;
+    for (int d = 1; d < 32; d <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += up;
+    }
+    int run = incl - s;
+    for (int i = lo; i < hi; i++) {
+      run += smaxc[i];
+      pre[i] = run;
+    }
+  }
+  __syncthreads();
+  // c. the trims as tile ranges
+  const int total = J > 0 ? pre[J - 1] : 0;
+  for (int j = tid; j < J; j += kThreads) {
+    const int gmax = grows[j].gmax;
+    const int gt = min(gmax, W - 1);
+    const int p = pre[j];
+    const int klim = min(K, p);                 // saturation point of the row
+    const int klo = max(0, K - (total - p));    // cone: the lowest k the backtrack can reach in this row
+    const int klimNext = j + 1 < J ? min(K, pre[j + 1]) : K;  // how far the next row (or P[J][K]) reads
+    const int tc0 = max(0, (klo + kCells - 1) / kCells - 1);  // first tile with a cell >= klo
+    int tcE = klim >= 1 ? min(KT, (klim - 1) / kCells + 1) : 0;  // one past the last tile starting at or below klim
+    if (tcE < tc0) tcE = tc0;
+    int fillE = klimNext >= 1 ? min(KT, (klimNext - 1) / kCells + 1) : 0;
+    if (fillE < tcE) fillE = tcE;
+    rowq[j] = pack_row(gt > 0 ? (gt + 3) >> 2 : 0, gmax >= max(W, 1), tc0, tcE, fillE);
+    grows[j].klim = klim;
+  }
+  __syncthreads();
+}
 
 // All DP rows of one round.  Returns with the last row in `*last` (shared memory).
-__device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, int K, int KT, int SW,
-                          const FfdlScratch& sc, int rr, const float4** last) {
+__device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT, int SW, float* __restrict__ slab,
+                          size_t rowFloats, const float* gs, FfdlRow* grows,
+                          const float4** last) {
   const int tid = threadIdx.x;
-  const int W = a.stride;
   float4* prev = sm.rowA;
   float4* cur = sm.rowB;
-  float* slab = sc.P + (size_t)rr * sc.slabFloats;
-  float* gsrows = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)SW;
-  FfdlRow* grows = sc.rows + (size_t)rr * (size_t)sc.Jcap;
   // row 0: P[0][k] = 0 for every k (:80-82)
-  for (int q = tid; q <= (kCells / 4) * KT; q += kThreads)
+  for (int q = tid; q <= 2 * KT; q += kThreads)
     prev[q] = q == 0 ? make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, 0.0f) : make_float4(0.f, 0.f, 0.f, 0.f);
-  // stage S of row 1
-  auto s_value = [&](int j, int g) -> float {  // value of srow slot g-1 for sorted job j (1-based)
-    const int mx = sm.smax[j - 1];
-    const int gt = min(min(mx, K), W - 1);  // last g served from the table loop
-    if (g > gt) return VODA_NEG_INF;
-    const int job = o + sm.perm[j - 1];
-    const size_t row = a.sp_off ? (size_t)a.sp_off[job] : (size_t)job * (size_t)W;
-    return a.speedup[row + (size_t)g];
+  const unsigned long long* rowq = reinterpret_cast<const unsigned long long*>(sm.khi);
+  const float* srmax = reinterpret_cast<const float*>(sm.klo);
+  // S rows reach shared memory through a four-slot ring filled by 16-byte asynchronous copies
+  // (cp.async: global -> shared without a register in between) issued TWO rows ahead: a row of
+  // the loop is shorter than an L2 round trip.
+  const int sGroups = SW / 4;
+  auto stage_s = [&](int row) {  // row: 0-based DP row whose S goes to slot row & 3
+    if (tid < sGroups && row < J)
+      cp_async16(sm.sring + (size_t)(row & 3) * sGroups + tid, reinterpret_cast<const float4*>(gs + (size_t)row * SW) + tid);
+    cp_async_commit();
   };
-  if (J >= 1)
-    for (int g = tid + 1; g <= SW; g += kThreads) {
-      const float s1 = s_value(1, g);
-      sm.srow1[g - 1] = s1;
-      gsrows[g - 1] = s1;
-    }
+  stage_s(0);
+  stage_s(1);
+  cp_async_wait<0>();
   __syncthreads();
+  const int sB = SW >= 8 ? 1 : 0;  // SW >= 4: the second block is clamped
   float cprev = 0.0f;  // c_0: P[0][k] = 0
   for (int j = 1; j <= J; j++) {
-    const float* srow = (j & 1) ? sm.srow1 : sm.srow0;
-    float* snext = (j & 1) ? sm.srow0 : sm.srow1;
-    // software-pipelined prefetch of the next row's S values (global -> register -> smem)
-    float pre[2] = {VODA_NEG_INF, VODA_NEG_INF};
-    if (j < J) {
-#pragma unroll
-      for (int u = 0; u < 2; u++) {
-        int g = tid + 1 + u * kThreads;
-        if (g <= SW) pre[u] = s_value(j + 1, g);
-      }
-    }
-    const int mx = sm.smax[j - 1];
-    const int gmax = min(mx, K);
-    const int gt = min(gmax, W - 1);
-    const int nblk = gt > 0 ? (gt + 3) >> 2 : 0;
-    const int klim = sm.scum[j - 1];
-    const int klo = sm.slo[j - 1];
+    const unsigned long long rq = rowq[j - 1];
+    stage_s(j + 1);  // its slot was last read two barriers ago
+    const float4* s4 = sm.sring + (size_t)((j - 1) & 3) * sGroups;
+    const float4 sA = s4[0], sBv = s4[sB];
+    const int nblk = (int)(rq & 0x7fff);
+    const bool slow = (rq & 0x8000) != 0;
+    const int tc0 = (int)((rq >> 16) & 0xffff), tcE = (int)((rq >> 32) & 0xffff), fillE = (int)(rq >> 48);
     // c_j = max(-10000, max_g (S_j[g] + c_{j-1})) = max(-10000, (max_g S_j[g]) + c_{j-1}): rounding
     // is monotone, so the maximum commutes with the addition exactly
-    const float ccur = fmaxf(-10000.0f, sm.srmax[j - 1] + cprev);
-    if (tid == 0) grows[j - 1] = FfdlRow{sm.perm[j - 1], gmax, klim, ccur};
-    for (int tq = tid; tq < KT; tq += kThreads) {
-      if (kCells * tq + kCells < klo) continue;
-      if (kCells * tq + 1 > klim) {
-        const float4 c4 = make_float4(ccur, ccur, ccur, ccur);
-#pragma unroll
-        for (int i = 0; i < kCells / 4; i++) cur[(kCells / 4) * tq + 1 + i] = c4;
-      } else {
-        ffdl_row_tile(prev, cur, srow, tq, nblk, max(W, 1), gmax);
+    const float ccur = fmaxf(-10000.0f, srmax[j - 1] + cprev);
+    if (tid == 0) grows[j - 1].c = ccur;
+    if (!slow && nblk == 1) {
+      for (int tq = tc0 + tid; tq < tcE; tq += kThreads) ffdl_tile_nb<1>(prev, cur, tq, sA, sBv);
+    } else if (!slow && nblk == 2) {
+      for (int tq = tc0 + tid; tq < tcE; tq += kThreads) ffdl_tile_nb<2>(prev, cur, tq, sA, sBv);
+    } else {
+      const int gslow1 = slow ? grows[j - 1].gmax : -1;  // written by this CTA before the last barrier
+      for (int tq = tc0 + tid; tq < tcE; tq += kThreads)
+        ffdl_tile_any(prev, cur, tq, s4, nblk, max(a.stride, 1), gslow1);
+    }
+    {
+      const float4 c4 = make_float4(ccur, ccur, ccur, ccur);
+      for (int tq = tcE + tid; tq < fillE; tq += kThreads) {
+        cur[2 * tq + 1] = c4;
+        cur[2 * tq + 2] = c4;
       }
     }
     cprev = ccur;
     if (tid == 0) cur[0] = make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, -10000.0f);  // P[j][0]
-    if (j < J) {
-      float* gs = gsrows + (size_t)j * (size_t)SW;
-#pragma unroll
-      for (int u = 0; u < 2; u++) {
-        int g = tid + 1 + u * kThreads;
-        if (g <= SW) {
-          snext[g - 1] = pre[u];
-          gs[g - 1] = pre[u];
-        }
-      }
-      for (int g = tid + 1 + 2 * kThreads; g <= SW; g += kThreads) {
-        const float s2 = s_value(j + 1, g);
-        snext[g - 1] = s2;
-        gs[g - 1] = s2;
-      }
-    }
     // Row j goes to the round's slab as ONE bulk copy (shared -> global, issued by thread 0 and
     // carried out by the copy engine while the CTA computes row j+1 from the same buffer), so the
     // store costs the threads neither issue slots nor LSU cycles.  The copy of row j-1 has had a
     // whole row of compute to finish reading its buffer, which row j+1 is about to overwrite.
     fence_proxy_async_smem();
     if (tid == 0) bulk_wait_read();
+    cp_async_wait<1>();  // everything but this row's stage_s has landed: the next row's S is in its slot
     __syncthreads();
-    if (tid == 0 && j < J) {
-      const int tlo = max(0, (klo + kCells - 1) / kCells - 1);  // first tile with a cell >= klo
-      const int thi = min(KT - 1, (klim - 1) / kCells);         // last tile that starts at or below klim
-      if (klim >= 1 && thi >= tlo) {
-        const int q0 = (kCells / 4) * tlo;
-        bulk_store(slab + (size_t)(j - 1) * sc.rowFloats + (size_t)q0 * 4, cur + q0 + 1,
-                   (uint32_t)(thi - tlo + 1) * kCells * 4u);
-      }
-    }
+    if (tid == 0 && j < J && tcE > tc0)  // row J is only read at [K], from shared memory
+      bulk_store(slab + (size_t)(j - 1) * rowFloats + (size_t)tc0 * kCells, cur + 2 * tc0 + 1,
+                 (uint32_t)(tcE - tc0) * kCells * 4u);
     float4* t = prev;
     prev = cur;
     cur = t;
@@ -311,17 +367,11 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
     const int pad = pad_groups(SW);
     sm.rowA = reinterpret_cast<float4*>(p) + pad; p += sizeof(float4) * (size_t)(pad + K4cap + 1);
     sm.rowB = reinterpret_cast<float4*>(p) + pad; p += sizeof(float4) * (size_t)(pad + K4cap + 1);
-    sm.srow0 = reinterpret_cast<float*>(p); p += sizeof(float) * (size_t)SW;
-    sm.srow1 = reinterpret_cast<float*>(p); p += sizeof(float) * (size_t)SW;
+    sm.sring = reinterpret_cast<float4*>(p); p += sizeof(float) * 4 * (size_t)SW;
     sm.khi = reinterpret_cast<int64_t*>(p); p += sizeof(int64_t) * (size_t)Jp;
-    sm.red = reinterpret_cast<long long*>(p); p += sizeof(long long) * 2;
     sm.klo = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
     sm.perm = reinterpret_cast<int*>(p); p += sizeof(int) * (size_t)Jp;
-    sm.smax = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
-    sm.scum = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
-    sm.slo = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
-    sm.srmax = reinterpret_cast<float*>(p); p += sizeof(float) * (size_t)Jp;
-    sm.misc = reinterpret_cast<int*>(p);
+    sm.pre = reinterpret_cast<int32_t*>(p);
   }
   const int tid = threadIdx.x;
   for (int q = tid; q < pad_groups(SW); q += kThreads) {  // written once: nothing else stores there
@@ -359,37 +409,14 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
     }
     __syncthreads();
     block_argsort(sm.khi, sm.klo, sm.perm, n, next_pow2(n));
-    // 2. trim
+    // 2. trim, 3-4. DP rows
     const int J = min(n, K);
-    for (int j = tid; j < J; j += kThreads) {
-      const int pj = sm.perm[j];
-      const int mx = a.max_proc[o + pj];
-      sm.smax[j] = mx;
-      // largest speedup value the row can use (g beyond the table reads 0: a Go map miss)
-      const int gmx = min(mx, K);
-      float rm = gmx >= max(a.stride, 1) ? 0.0f : VODA_NEG_INF;
-      const float* sj = a.speedup + (a.sp_off ? (size_t)a.sp_off[o + pj] : (size_t)(o + pj) * (size_t)a.stride);
-      for (int g = 1; g <= min(gmx, a.stride - 1); g++) rm = fmaxf(rm, sj[g]);
-      sm.srmax[j] = rm;
-    }
-    __syncthreads();
-    if (tid == 0) {  // the two running sums of the usable sizes (short serial scans)
-      long long acc = 0;
-      for (int j = 0; j < J; j++) {
-        acc += max(0, min(sm.smax[j], K));
-        sm.scum[j] = (int)min(acc, (long long)K);
-      }
-      acc = 0;
-      for (int j = J - 1; j >= 0; j--) {
-        sm.slo[j] = (int)max(0LL, (long long)K - acc);
-        acc += max(0, min(sm.smax[j], K));
-      }
-    }
-    __syncthreads();
-    // 3-4. DP rows
     const int KT = (K + kCells - 1) / kCells;
+    float* gs = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)SW;
+    FfdlRow* grows = sc.rows + (size_t)rr * (size_t)sc.Jcap;
+    ffdl_setup_rows(a, sm, o, J, K, KT, SW, gs, grows);
     const float4* last = nullptr;
-    ffdl_rows(a, sm, o, J, K, KT, SW, sc, rr, &last);
+    ffdl_rows(a, sm, J, KT, SW, sc.P + (size_t)rr * sc.slabFloats, sc.rowFloats, gs, grows, &last);
     const float PJK = reinterpret_cast<const float*>(last)[K + 3];
     meta.J = J;
     if (PJK <= 0.0f) meta.st = VODA_ST_INFEASIBLE;  // :109-114 (NaN is not <= 0, as in Go)
@@ -538,8 +565,8 @@ static void ffdl_shape(const AllocArgs& a, int* K4cap, int* SW, int* Jp, size_t*
   if (sw < 1) sw = 1;
   *SW = (sw + 3) & ~3;
   *Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  *smem = sizeof(float4) * 2 * (size_t)(pad_groups(*SW) + *K4cap + 1) + sizeof(float) * 2 * (size_t)(*SW) +
-          (sizeof(int64_t) + 6 * sizeof(int32_t)) * (size_t)(*Jp) + 2 * sizeof(long long) + 4 * sizeof(int);
+  *smem = sizeof(float4) * 2 * (size_t)(pad_groups(*SW) + *K4cap + 1) + sizeof(float) * 4 * (size_t)(*SW) +
+          (sizeof(int64_t) + 3 * sizeof(int32_t)) * (size_t)(*Jp);
 }
 
 static size_t ffdl_jcap(const AllocArgs& a) {
