@@ -64,8 +64,8 @@ __device__ __forceinline__ unsigned long long pack_row(int nblk, bool slow, int 
 // Shared memory per CTA: two row buffers and 20 bytes per job; the sort keys' space is reused
 // for the row constants once the sort is done.
 struct FfdlSmem {
-  float4* rowA;    // [pad + G4]  row buffers, group q = P[4q-3 .. 4q], -inf groups in front
-  float4* rowB;    // [pad + G4]
+  float4* rowA;    // row buffers (see Row below); the pointer is E[0]
+  float4* rowB;
   int64_t* khi;    // [Jp]  sort key (seconds); after the sort: the packed row constants
   int32_t* klo;    // [Jp]  sort key (nanoseconds); after the sort: srmax, max over the row's usable g of S_j[g]
   int* perm;       // [Jp]  sorted position -> job; then smaxc = clamp(max_proc, 0, K) in sorted order
@@ -93,15 +93,29 @@ struct FfdlScratch {
   FfdlRow* rows;      // [count][Jcap]
   float* srows;       // [count][Jcap][SW]  S rows in sorted order, -inf beyond the table limit
   float* P;           // [count][Jcap][rowFloats]  P[j][1..K]: row j-1, float k-1
-  size_t rowFloats;   // 4 * K4cap
+  size_t rowFloats;   // 8 * KTcap
   size_t slabFloats;  // Jcap * rowFloats
   int Jcap;
   int SW;
 };
 
-// Row buffers carry pad_groups(SW) groups of -inf in front of group 0, so the window can slide
-// left of the row (k-g < 0) without a branch.
-__host__ __device__ constexpr int pad_groups(int SW) { return SW / 4 + 1; }
+// A DP row in shared memory.  Group q holds P[4q-3 .. 4q] (group 0 = three cells left of the
+// row and P[j][0]).  A thread's tile is two groups (2tq+1, 2tq+2) and its window three
+// (2tq .. 2tq+2), so with the groups stored in order the lanes of a warp would touch every
+// other 16 bytes: a two-way bank conflict on every LDS.128 / STS.128.  The groups are therefore
+// stored DE-INTERLEAVED: the even groups E[i] = group 2i in one array, the odd groups
+// O[i] = group 2i+1 in another (O = E + ost), and consecutive lanes touch consecutive 16 bytes.
+// Both arrays carry pad_half(SW) groups of -inf in front, so the window can slide left of the
+// row (k-g < 0) without a branch.
+__host__ __device__ constexpr int pad_half(int SW) { return (SW / 4 + 1) / 2 + 1; }
+__host__ __device__ constexpr int row_groups(int SW, int KTcap) { return 2 * pad_half(SW) + 2 * KTcap + 2; }
+__device__ __forceinline__ const float4* grp(const float4* E, int ost, int q) {
+  return E + (q >> 1) + ((q & 1) ? ost : 0);
+}
+__device__ __forceinline__ float cell(const float4* E, int ost, int x) {  // P[x], x >= 0
+  return reinterpret_cast<const float*>(grp(E, ost, (x + 3) >> 2))[(x + 3) & 3];
+}
+
 
 // 4 g-steps (g = 4m+1 .. 4m+4) for the 8 cells of a tile: cell c at step s reads element
 // 3+c-s of the window (lo, mid, hi) = 12 consecutive floats of row j-1; two candidates per
@@ -116,79 +130,76 @@ __device__ __forceinline__ void ffdl_block8(float (&best)[8], const float4 sq, c
   }
 }
 
-__device__ __forceinline__ void ffdl_store_tile(float4* __restrict__ cur, int qtop, const float (&best)[8]) {
-  cur[qtop + 1] = make_float4(best[0], best[1], best[2], best[3]);
-  cur[qtop + 2] = make_float4(best[4], best[5], best[6], best[7]);
+__device__ __forceinline__ void ffdl_store_tile(float4* __restrict__ cur, int ost, int tq, const float (&best)[8],
+                                                float4* __restrict__ grow) {
+  const float4 lo = make_float4(best[0], best[1], best[2], best[3]);
+  const float4 hi = make_float4(best[4], best[5], best[6], best[7]);
+  cur[tq + ost] = lo;  // group 2tq+1
+  cur[tq + 1] = hi;    // group 2tq+2
+  if (grow) {  // the slab row is in cell order; streamed: nothing reads it before the backtrack kernel
+    __stcs(grow + 2 * tq, lo);
+    __stcs(grow + 2 * tq + 1, hi);
+  }
 }
 
 // One DP row for column tile `tq` (cells k = 8*tq+1 .. 8*tq+8) when every candidate comes from
 // the first NB blocks of the table (g <= 4*NB): the common shapes, fully unrolled, S in registers.
-// Row storage: group q = P[4q-3 .. 4q].  For the block of g = 4m+1 .. 4m+4 the cells need
-// P[base-3 .. base+8], base = 8*tq - 4m, i.e. groups q0 .. q0+2 with q0 = 2*tq - m.
+// For the block of g = 4m+1 .. 4m+4 the cells need P[base-3 .. base+8], base = 8*tq - 4m, i.e.
+// groups q0 .. q0+2 with q0 = 2*tq - m.
 template <int NB>
-__device__ __forceinline__ void ffdl_tile_nb(const float4* __restrict__ prev, float4* __restrict__ cur, int tq,
-                                             const float4 sA, const float4 sB) {
+__device__ __forceinline__ void ffdl_tile_nb(const float4* __restrict__ prev, float4* __restrict__ cur, int ost,
+                                             int tq, const float4 sA, const float4 sB, float4* __restrict__ grow) {
   float best[8];
 #pragma unroll
   for (int c = 0; c < 8; c++) best[c] = -10000.0f;
-  const int qtop = 2 * tq;
-  const float4 g0 = prev[qtop], g1 = prev[qtop + 1], g2 = prev[qtop + 2];
+  const float4 g0 = prev[tq], g1 = prev[tq + ost], g2 = prev[tq + 1];
   ffdl_block8(best, sA, g0, g1, g2);
   if (NB >= 2) {
-    const float4 gm = prev[qtop - 1];
+    const float4 gm = prev[tq - 1 + ost];
     ffdl_block8(best, sB, gm, g0, g1);
   }
-  ffdl_store_tile(cur, qtop, best);
+  ffdl_store_tile(cur, ost, tq, best, grow);
 }
 
 // The general tile: any number of blocks (S read from the round's sorted S rows in global
 // memory), then the candidates g in [gslow0, gslow1] the dense table does not hold (the Go map
 // misses, S = 0; rare: max_j >= W).
-__device__ __forceinline__ void ffdl_tile_any(const float4* __restrict__ prev, float4* __restrict__ cur, int tq,
-                                              const float4* __restrict__ s4, int nblk, int gslow0, int gslow1) {
+__device__ __forceinline__ void ffdl_tile_any(const float4* __restrict__ prev, float4* __restrict__ cur, int ost,
+                                              int tq, const float4* __restrict__ s4, int nblk, int gslow0,
+                                              int gslow1, float4* __restrict__ grow) {
   float best[8];
 #pragma unroll
   for (int c = 0; c < 8; c++) best[c] = -10000.0f;
   const int qtop = 2 * tq;
   // the window is three groups; instead of shifting registers after every block the three
   // roles rotate through three unrolled copies of the block
-  float4 g0 = prev[qtop], g1 = prev[qtop + 1], g2 = prev[qtop + 2];
+  float4 g0 = *grp(prev, ost, qtop), g1 = *grp(prev, ost, qtop + 1), g2 = *grp(prev, ost, qtop + 2);
   int m = 0;
   for (; m + 3 <= nblk; m += 3) {
     ffdl_block8(best, s4[m], g0, g1, g2);
-    g2 = prev[qtop - m - 1];
+    g2 = *grp(prev, ost, qtop - m - 1);
     ffdl_block8(best, s4[m + 1], g2, g0, g1);
-    g1 = prev[qtop - m - 2];
+    g1 = *grp(prev, ost, qtop - m - 2);
     ffdl_block8(best, s4[m + 2], g1, g2, g0);
-    g0 = prev[qtop - m - 3];
+    g0 = *grp(prev, ost, qtop - m - 3);
   }
   if (m < nblk) {
     ffdl_block8(best, s4[m], g0, g1, g2);
     if (m + 1 < nblk) {
-      g2 = prev[qtop - m - 1];
+      g2 = *grp(prev, ost, qtop - m - 1);
       ffdl_block8(best, s4[m + 1], g2, g0, g1);
     }
   }
   if (gslow1 >= gslow0) {
-    const float* pf = reinterpret_cast<const float*>(prev);
 #pragma unroll
     for (int c = 0; c < 8; c++) {
       const int k = 8 * tq + 1 + c;
-      for (int g = gslow0; g <= gslow1 && g <= k; g++) best[c] = fmaxf(best[c], 0.0f + pf[k - g + 3]);
+      for (int g = gslow0; g <= gslow1 && g <= k; g++) best[c] = fmaxf(best[c], 0.0f + cell(prev, ost, k - g));
     }
   }
-  ffdl_store_tile(cur, qtop, best);
+  ffdl_store_tile(cur, ost, tq, best, grow);
 }
 
-// Bulk asynchronous copy shared -> global (cp.async.bulk, the TMA engine without a tensor map).
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-__device__ __forceinline__ void bulk_store(float* dst, const float4* src, uint32_t bytes) {
-  const uint32_t s = (uint32_t)__cvta_generic_to_shared(src);
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(s), "r"(bytes) : "memory");
-  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-}
-__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 // 16-byte asynchronous copy global -> shared (LDGSTS)
 __device__ __forceinline__ void cp_async16(float4* dst, const float4* src) {
   const uint32_t d = (uint32_t)__cvta_generic_to_shared(dst);
@@ -281,36 +292,48 @@ __device__ void ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, i
 }
 
 // All DP rows of one round.  Returns with the last row in `*last` (shared memory).
-__device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT, int SW, float* __restrict__ slab,
-                          size_t rowFloats, const float* gs, FfdlRow* grows,
+__device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT, int SW, int ost,
+                          float* __restrict__ slab, size_t rowFloats, const float* gs, FfdlRow* grows,
                           const float4** last) {
   const int tid = threadIdx.x;
   float4* prev = sm.rowA;
   float4* cur = sm.rowB;
   // row 0: P[0][k] = 0 for every k (:80-82)
-  for (int q = tid; q <= 2 * KT; q += kThreads)
-    prev[q] = q == 0 ? make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, 0.0f) : make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int i = tid; i <= KT; i += kThreads) {
+    prev[i] = i == 0 ? make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, 0.0f) : make_float4(0.f, 0.f, 0.f, 0.f);
+    prev[i + ost] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   const unsigned long long* rowq = reinterpret_cast<const unsigned long long*>(sm.khi);
   const float* srmax = reinterpret_cast<const float*>(sm.klo);
   // S rows reach shared memory through a four-slot ring filled by 16-byte asynchronous copies
   // (cp.async: global -> shared without a register in between) issued TWO rows ahead: a row of
-  // the loop is shorter than an L2 round trip.
+  // the loop is shorter than an L2 round trip.  Everything that advances by a constant per row
+  // is a running pointer (the row loop is short enough for its address arithmetic to show).
   const int sGroups = SW / 4;
-  auto stage_s = [&](int row) {  // row: 0-based DP row whose S goes to slot row & 3
-    if (tid < sGroups && row < J)
-      cp_async16(sm.sring + (size_t)(row & 3) * sGroups + tid, reinterpret_cast<const float4*>(gs + (size_t)row * SW) + tid);
+  const bool stager = tid < sGroups;
+  const float4* sgp = reinterpret_cast<const float4*>(gs) + tid;  // S row to stage next, this thread's 16 bytes
+  float4* ringt = sm.sring + tid;
+  int stageRow = 0;
+  auto stage_s = [&]() {  // the S row of DP row stageRow (0-based) goes to slot stageRow & 3
+    if (stager && stageRow < J) cp_async16(ringt + (stageRow & 3) * sGroups, sgp);
     cp_async_commit();
+    sgp += sGroups;
+    stageRow++;
   };
-  stage_s(0);
-  stage_s(1);
+  stage_s();
+  stage_s();
   cp_async_wait<0>();
   __syncthreads();
   const int sB = SW >= 8 ? 1 : 0;  // SW >= 4: the second block is clamped
+  const int gslow0 = max(a.stride, 1);
   float cprev = 0.0f;  // c_0: P[0][k] = 0
-  for (int j = 1; j <= J; j++) {
+  float4* grow = reinterpret_cast<float4*>(slab);  // row j of P goes to slab row j-1
+  const size_t rowGroups = rowFloats / 4;
+  FfdlRow* gr = grows;
+  for (int j = 1; j <= J; j++, grow += rowGroups, gr++) {
     const unsigned long long rq = rowq[j - 1];
-    stage_s(j + 1);  // its slot was last read two barriers ago
-    const float4* s4 = sm.sring + (size_t)((j - 1) & 3) * sGroups;
+    stage_s();  // row j+1; its slot was last read two barriers ago
+    const float4* s4 = sm.sring + ((j - 1) & 3) * sGroups;
     const float4 sA = s4[0], sBv = s4[sB];
     const int nblk = (int)(rq & 0x7fff);
     const bool slow = (rq & 0x8000) != 0;
@@ -318,55 +341,46 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT,
     // c_j = max(-10000, max_g (S_j[g] + c_{j-1})) = max(-10000, (max_g S_j[g]) + c_{j-1}): rounding
     // is monotone, so the maximum commutes with the addition exactly
     const float ccur = fmaxf(-10000.0f, srmax[j - 1] + cprev);
-    if (tid == 0) grows[j - 1].c = ccur;
+    if (tid == 0) gr->c = ccur;
+    float4* gdst = j < J ? grow : nullptr;  // row J is only read at [K], from shared memory
     if (!slow && nblk == 1) {
-      for (int tq = tc0 + tid; tq < tcE; tq += kThreads) ffdl_tile_nb<1>(prev, cur, tq, sA, sBv);
+      for (int tq = tc0 + tid; tq < tcE; tq += kThreads) ffdl_tile_nb<1>(prev, cur, ost, tq, sA, sBv, gdst);
     } else if (!slow && nblk == 2) {
-      for (int tq = tc0 + tid; tq < tcE; tq += kThreads) ffdl_tile_nb<2>(prev, cur, tq, sA, sBv);
+      for (int tq = tc0 + tid; tq < tcE; tq += kThreads) ffdl_tile_nb<2>(prev, cur, ost, tq, sA, sBv, gdst);
     } else {
-      const int gslow1 = slow ? grows[j - 1].gmax : -1;  // written by this CTA before the last barrier
+      const int gslow1 = slow ? gr->gmax : -1;  // written by this CTA before the last barrier
       for (int tq = tc0 + tid; tq < tcE; tq += kThreads)
-        ffdl_tile_any(prev, cur, tq, s4, nblk, max(a.stride, 1), gslow1);
+        ffdl_tile_any(prev, cur, ost, tq, s4, nblk, gslow0, gslow1, gdst);
     }
     {
       const float4 c4 = make_float4(ccur, ccur, ccur, ccur);
       for (int tq = tcE + tid; tq < fillE; tq += kThreads) {
-        cur[2 * tq + 1] = c4;
-        cur[2 * tq + 2] = c4;
+        cur[tq + ost] = c4;
+        cur[tq + 1] = c4;
       }
     }
     cprev = ccur;
     if (tid == 0) cur[0] = make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, -10000.0f);  // P[j][0]
-    // Row j goes to the round's slab as ONE bulk copy (shared -> global, issued by thread 0 and
-    // carried out by the copy engine while the CTA computes row j+1 from the same buffer), so the
-    // store costs the threads neither issue slots nor LSU cycles.  The copy of row j-1 has had a
-    // whole row of compute to finish reading its buffer, which row j+1 is about to overwrite.
-    fence_proxy_async_smem();
-    if (tid == 0) bulk_wait_read();
     cp_async_wait<1>();  // everything but this row's stage_s has landed: the next row's S is in its slot
     __syncthreads();
-    if (tid == 0 && j < J && tcE > tc0)  // row J is only read at [K], from shared memory
-      bulk_store(slab + (size_t)(j - 1) * rowFloats + (size_t)tc0 * kCells, cur + 2 * tc0 + 1,
-                 (uint32_t)(tcE - tc0) * kCells * 4u);
     float4* t = prev;
     prev = cur;
     cur = t;
   }
-  if (tid == 0) bulk_wait_all();
   *last = prev;
 }
 
 // Kernel A: sort + DP rows.  One CTA per round at a time; P rows / row records / meta go to the
 // round's own slot of the scratch so that the CTA can move on to its next round immediately.
 __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
-    ffdl_dp_kernel(AllocArgs a, int r0, int count, FfdlScratch sc, int K4cap, int SW, int Jp) {
+    ffdl_dp_kernel(AllocArgs a, int r0, int count, FfdlScratch sc, int KTcap, int SW, int Jp) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   FfdlSmem sm;
   {
     unsigned char* p = smem_raw;
-    const int pad = pad_groups(SW);
-    sm.rowA = reinterpret_cast<float4*>(p) + pad; p += sizeof(float4) * (size_t)(pad + K4cap + 1);
-    sm.rowB = reinterpret_cast<float4*>(p) + pad; p += sizeof(float4) * (size_t)(pad + K4cap + 1);
+    const int ph = pad_half(SW);
+    sm.rowA = reinterpret_cast<float4*>(p) + ph; p += sizeof(float4) * (size_t)row_groups(SW, KTcap);
+    sm.rowB = reinterpret_cast<float4*>(p) + ph; p += sizeof(float4) * (size_t)row_groups(SW, KTcap);
     sm.sring = reinterpret_cast<float4*>(p); p += sizeof(float) * 4 * (size_t)SW;
     sm.khi = reinterpret_cast<int64_t*>(p); p += sizeof(int64_t) * (size_t)Jp;
     sm.klo = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
@@ -374,10 +388,13 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
     sm.pre = reinterpret_cast<int32_t*>(p);
   }
   const int tid = threadIdx.x;
-  for (int q = tid; q < pad_groups(SW); q += kThreads) {  // written once: nothing else stores there
+  const int ost = pad_half(SW) + KTcap + 1;  // O[i] = E[i + ost]
+  for (int q = tid; q < pad_half(SW); q += kThreads) {  // written once: nothing else stores there
     const float4 ninf = make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF);
     sm.rowA[-1 - q] = ninf;
+    sm.rowA[-1 - q + ost] = ninf;
     sm.rowB[-1 - q] = ninf;
+    sm.rowB[-1 - q + ost] = ninf;
   }
 
   for (int rr = blockIdx.x; rr < count; rr += gridDim.x) {
@@ -416,8 +433,8 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
     FfdlRow* grows = sc.rows + (size_t)rr * (size_t)sc.Jcap;
     ffdl_setup_rows(a, sm, o, J, K, KT, SW, gs, grows);
     const float4* last = nullptr;
-    ffdl_rows(a, sm, J, KT, SW, sc.P + (size_t)rr * sc.slabFloats, sc.rowFloats, gs, grows, &last);
-    const float PJK = reinterpret_cast<const float*>(last)[K + 3];
+    ffdl_rows(a, sm, J, KT, SW, ost, sc.P + (size_t)rr * sc.slabFloats, sc.rowFloats, gs, grows, &last);
+    const float PJK = cell(last, ost, K);
     meta.J = J;
     if (PJK <= 0.0f) meta.st = VODA_ST_INFEASIBLE;  // :109-114 (NaN is not <= 0, as in Go)
     if (tid == 0) sc.meta[rr] = meta;
@@ -558,14 +575,14 @@ __global__ void __launch_bounds__(kBtThreads)
 
 }  // namespace
 
-static void ffdl_shape(const AllocArgs& a, int* K4cap, int* SW, int* Jp, size_t* smem) {
+static void ffdl_shape(const AllocArgs& a, int* KTcap, int* SW, int* Jp, size_t* smem) {
   const int Kmax = a.max_total > 0 ? a.max_total : 1;
-  *K4cap = (kCells / 4) * ((Kmax + kCells - 1) / kCells);  // row groups of 4 cells, whole tiles
+  *KTcap = (Kmax + kCells - 1) / kCells;  // whole tiles
   int sw = a.stride - 1 < Kmax ? a.stride - 1 : Kmax;
   if (sw < 1) sw = 1;
   *SW = (sw + 3) & ~3;
   *Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  *smem = sizeof(float4) * 2 * (size_t)(pad_groups(*SW) + *K4cap + 1) + sizeof(float) * 4 * (size_t)(*SW) +
+  *smem = sizeof(float4) * 2 * (size_t)row_groups(*SW, *KTcap) + sizeof(float) * 4 * (size_t)(*SW) +
           (sizeof(int64_t) + 3 * sizeof(int32_t)) * (size_t)(*Jp);
 }
 
@@ -577,26 +594,26 @@ static size_t ffdl_jcap(const AllocArgs& a) {
 // Scratch one round needs: its P slab, the sorted S rows, the row records and the meta record
 // (every part a multiple of 16 bytes).
 size_t ffdl_scratch_per_round(const AllocArgs& a) {
-  int K4cap, SW, Jp;
+  int KTcap, SW, Jp;
   size_t smem;
-  ffdl_shape(a, &K4cap, &SW, &Jp, &smem);
+  ffdl_shape(a, &KTcap, &SW, &Jp, &smem);
   const size_t Jcap = ffdl_jcap(a);
-  return Jcap * (size_t)K4cap * 16 + Jcap * (size_t)SW * 4 + Jcap * sizeof(FfdlRow) + sizeof(FfdlMeta);
+  return Jcap * (size_t)KTcap * 32 + Jcap * (size_t)SW * 4 + Jcap * sizeof(FfdlRow) + sizeof(FfdlMeta);
 }
 
 size_t ffdl_smem_bytes(const AllocArgs& a) {
-  int K4cap, SW, Jp;
+  int KTcap, SW, Jp;
   size_t smem;
-  ffdl_shape(a, &K4cap, &SW, &Jp, &smem);
+  ffdl_shape(a, &KTcap, &SW, &Jp, &smem);
   return smem;
 }
 
 // Rounds [r0, r0+count) of `a`: DP kernel then backtrack kernel.  `scratch` must hold
 // count * ffdl_scratch_per_round(a) bytes (256-byte aligned).
 cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* scratch, cudaStream_t stream) {
-  int K4cap, SW, Jp;
+  int KTcap, SW, Jp;
   size_t smem;
-  ffdl_shape(a, &K4cap, &SW, &Jp, &smem);
+  ffdl_shape(a, &KTcap, &SW, &Jp, &smem);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(ffdl_dp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -604,7 +621,7 @@ cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* sc
   const size_t Jcap = ffdl_jcap(a);
   FfdlScratch sc;
   unsigned char* base = static_cast<unsigned char*>(scratch);
-  sc.rowFloats = (size_t)K4cap * 4;
+  sc.rowFloats = (size_t)KTcap * 8;
   sc.slabFloats = Jcap * sc.rowFloats;
   sc.Jcap = (int)Jcap;
   sc.SW = SW;
@@ -619,7 +636,7 @@ cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* sc
   if (perSm < 1) perSm = 1;
   int grid = sms * perSm;
   if (count < grid) grid = count;
-  ffdl_dp_kernel<<<grid, kThreads, smem, stream>>>(a, r0, count, sc, K4cap, SW, Jp);
+  ffdl_dp_kernel<<<grid, kThreads, smem, stream>>>(a, r0, count, sc, KTcap, SW, Jp);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const int perBlock = (kBtThreads / 32) * kBtRounds;  // rounds per block: eight lanes per round
