@@ -81,7 +81,7 @@ struct FfdlMeta {
   int32_t pad;
 };
 // ... and per DP row j (1-based; record j-1), 16 bytes so that one load fetches it
-struct FfdlRow {
+struct __align__(16) FfdlRow {
   int32_t job;   // index of the row's job within the round (input order)
   int32_t gmax;  // min(max_proc, K): candidates are g = 1 .. min(gmax, k)
   int32_t klim;  // saturation point of THIS row: P[j][k] == c for k >= klim
@@ -457,6 +457,9 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
 constexpr int kBtThreads = 128;
 constexpr int kBtLanes = 8;                  // lanes per round
 constexpr int kBtRounds = 32 / kBtLanes;     // rounds per warp
+constexpr int kBtAhead = 3;                  // rows of lookahead for the L2 prefetch of P
+
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
 __global__ void __launch_bounds__(kBtThreads)
     ffdl_backtrack_kernel(AllocArgs a, int r0, int count, FfdlScratch sc) {
@@ -488,6 +491,10 @@ __global__ void __launch_bounds__(kBtThreads)
           // one row ahead (none of this depends on the position)
           const FfdlRow rpp = j >= 3 ? grows[j - 3] : none;
           const float s1next = j >= 2 ? gsrows[(size_t)(j - 2) * SW + ssub] : 0.0f;
+          // the stretch of P the walk will read kBtAhead rows from now, pulled into L2: the position
+          // can only drift down, by the g's chosen on the way (four sectors cover 32 cells)
+          if (sub < 4 && j - 2 - kBtAhead >= 0)
+            prefetch_l2(slab + (size_t)(j - 2 - kBtAhead) * sc.rowFloats + max(k - 1 - 8 * sub, 0));
           const int gm = min(rc.gmax, k);  // k-g >= 0
           const float* sj = gsrows + (size_t)(j - 1) * SW;              // sj[g-1] = S_j[g]
           const float* prow = slab + (size_t)max(j - 2, 0) * sc.rowFloats;  // P[j-1][x] at prow[x-1] (j >= 2)
