@@ -442,141 +442,137 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
 }
 
 // Kernel B: backtrack (:116-125) + deferred validateResult (:42).
-// The walk is a chain of J dependent steps (row j-1 is read at k - g_j), so it is all latency,
-// and what it reads is scattered over the batch's slabs.  EIGHT LANES walk one round (four
-// rounds per warp, every round of the batch in flight at once): at row j they re-evaluate the
-// reference's inner loop (:93-103) for the single cell (j, k),
+// The walk is a chain of J dependent steps (row j-1 is read at k - g_j): it is all latency, and
+// its length per step is what the kernel's time is made of (measured: the same 0.4 ms for 2.5k,
+// 5k or 10k rounds).  ONE WARP walks one round, every round of the batch in flight at once.  At
+// row j the warp re-evaluates the reference's inner loop (:93-103) for the single cell (j, k),
 //   best = -10000, sol = 0;  for g = 1 .. min(max_j, K, k):  p = S_j[g] + P[j-1][k-g];
 //   if p > best { best = p; sol = g }
-// eight candidates at a time, one per lane: the eight P values are adjacent floats of the stored
-// row (one or two sectors per step instead of eight scattered requests), and the strict-'>'
-// scan becomes a three-step butterfly that keeps the larger value and, among equal values, the
-// smaller g.  P[j-1][x] comes from the stored row, its saturated constant, or row 0 = 0.
-// Only that load depends on the position: the row records and the S values of the next row are
-// fetched one row ahead.  Then the warp validates its four rounds with coalesced reads.
+// 32 candidates at a time, one per lane: the P values are adjacent floats of the stored row (one
+// coalesced load), and the strict-'>' scan in increasing g is "the first lane that holds the
+// maximum": an order-preserving integer key, one REDUX.MAX and one ballot.  P[j-1][x] comes
+// from the stored row, its saturated constant, or row 0 = 0.  Only that load depends on the
+// position: the row record and the S values of the next row are fetched one row ahead, and the
+// stretch of P the walk can reach a few rows from now is prefetched into L2.  Then the warp
+// validates its round with coalesced reads.
 constexpr int kBtThreads = 128;
-constexpr int kBtLanes = 8;                  // lanes per round
-constexpr int kBtRounds = 32 / kBtLanes;     // rounds per warp
-constexpr int kBtAhead = 3;                  // rows of lookahead for the L2 prefetch of P
+constexpr int kBtAhead = 3;  // rows of lookahead for the L2 prefetch of P
 
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 
+// Order-preserving map float -> unsigned (the usual sign flip), after folding -0 into +0 so that
+// equal floats get equal keys; NaN and "no such candidate" are mapped to key 0 by the caller.
+__device__ __forceinline__ unsigned f32_key(float p) {
+  const unsigned u = __float_as_uint(p + 0.0f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// LANES lanes walk one round: 32 (a warp per round, the shortest chain) while every round of
+// the launch fits on the GPU at once, 16 or 8 (two or four rounds per warp, whose walks diverge)
+// beyond.
+template <int LANES>
 __global__ void __launch_bounds__(kBtThreads)
     ffdl_backtrack_kernel(AllocArgs a, int r0, int count, FfdlScratch sc) {
-  const int lane = threadIdx.x & 31;
-  const int sub = lane & (kBtLanes - 1);
-  const int rr0 = (blockIdx.x * (kBtThreads / 32) + (threadIdx.x >> 5)) * kBtRounds;
-  if (rr0 >= count) return;
-  // ---- phase 1: one walk per group of eight lanes
-  {
-    const int rr = rr0 + lane / kBtLanes;
-    const unsigned gmask = ((1u << kBtLanes) - 1u) << (lane & ~(kBtLanes - 1));
-    if (rr < count) {
-      const int r = r0 + rr;
-      const int o = a.job_off[r] - a.job_base;
-      const FfdlMeta meta = sc.meta[rr];
-      if (meta.st == VODA_ST_OK && meta.J > 0) {
-        const float* slab = sc.P + (size_t)rr * sc.slabFloats;
-        const float* gsrows = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)sc.SW;
-        const FfdlRow* grows = sc.rows + (size_t)rr * (size_t)sc.Jcap;
-        const int SW = sc.SW;
-        const int W = a.stride;
-        const int ssub = min(sub, SW - 1);
-        const FfdlRow none{0, 0, 0, 0.0f};
-        int k = meta.K;
-        FfdlRow rc = grows[meta.J - 1];                      // row j
-        FfdlRow rp = meta.J >= 2 ? grows[meta.J - 2] : none;  // row j-1: its klim and c describe the row read
-        float s1 = gsrows[(size_t)(meta.J - 1) * SW + ssub];  // S_j[1 + sub]
-        for (int j = meta.J; j >= 1; j--) {
-          // one row ahead (none of this depends on the position)
-          const FfdlRow rpp = j >= 3 ? grows[j - 3] : none;
-          const float s1next = j >= 2 ? gsrows[(size_t)(j - 2) * SW + ssub] : 0.0f;
-          // the stretch of P the walk will read kBtAhead rows from now, pulled into L2: the position
-          // can only drift down, by the g's chosen on the way (four sectors cover 32 cells)
-          if (sub < 4 && j - 2 - kBtAhead >= 0)
-            prefetch_l2(slab + (size_t)(j - 2 - kBtAhead) * sc.rowFloats + max(k - 1 - 8 * sub, 0));
-          const int gm = min(rc.gmax, k);  // k-g >= 0
-          const float* sj = gsrows + (size_t)(j - 1) * SW;              // sj[g-1] = S_j[g]
-          const float* prow = slab + (size_t)max(j - 2, 0) * sc.rowFloats;  // P[j-1][x] at prow[x-1] (j >= 2)
-          float best = -10000.0f;
-          int sol = 0;
-          for (int g0 = 1; g0 <= gm; g0 += kBtLanes) {
-            const int g = g0 + sub;
-            const int x = k - g;
-            // unconditional loads on clamped, always-valid addresses; the cases are sorted out below
-            const float pv = prow[max(x, 1) - 1];
-            const float sv = g0 == 1 ? s1 : sj[min(g, SW) - 1];
-            const float sg = g <= W - 1 ? sv : 0.0f;  // a g the table does not hold: Go map miss
-            float pg = x <= 0 ? -10000.0f : (x >= rp.klim ? rp.c : pv);
-            if (j == 1) pg = 0.0f;  // row 0
-            float p = sg + pg;
-            if (g > gm || p != p) p = VODA_NEG_INF;  // no such candidate / NaN: can never win
-            int gg = g;
-#pragma unroll
-            for (int d = 1; d < kBtLanes; d <<= 1) {
-              const float po = __shfl_xor_sync(gmask, p, d);
-              const int go = __shfl_xor_sync(gmask, gg, d);
-              if (po > p || (po == p && go < gg)) {
-                p = po;
-                gg = go;
-              }
-            }
-            if (p > best) {
-              best = p;
-              sol = gg;
-            }
-          }
-          if (sub == 0) a.out_gpus[o + rc.job] = sol;
-          k -= sol;
-          rc = rp;
-          rp = rpp;
-          s1 = s1next;
+  const int wlane = threadIdx.x & 31;
+  const int lane = wlane & (LANES - 1);       // lane within the round's group
+  const int shift = wlane & ~(LANES - 1);     // first lane of the group
+  const unsigned full = LANES == 32 ? 0xffffffffu : (((1u << (LANES & 31)) - 1u) << shift);
+  const int rr = (blockIdx.x * (kBtThreads / 32) + (threadIdx.x >> 5)) * (32 / LANES) + wlane / LANES;
+  if (rr >= count) return;
+  const int r = r0 + rr;
+  const int o = a.job_off[r] - a.job_base;
+  const int n = a.job_off[r + 1] - a.job_off[r];
+  const FfdlMeta meta = sc.meta[rr];
+  // ---- phase 1: the walk
+  if (meta.st == VODA_ST_OK && meta.J > 0) {
+    const float* slab = sc.P + (size_t)rr * sc.slabFloats;
+    const float* gsrows = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)sc.SW;
+    const int4* grows = reinterpret_cast<const int4*>(sc.rows + (size_t)rr * (size_t)sc.Jcap);  // job, gmax, klim, c
+    int32_t* out = a.out_gpus + o;
+    const int SW = sc.SW;
+    const int W = a.stride;
+    const int rowFloats = (int)sc.rowFloats;
+    const int slane = min(lane, SW - 1);
+    const int4 none = make_int4(0, 0, 0, 0);
+    const unsigned keyFloor = f32_key(-10000.0f);
+    const int J = meta.J;
+    int k = meta.K;
+    int4 rc = grows[J - 1];                  // row j
+    int4 rp = J >= 2 ? grows[J - 2] : none;  // row j-1: its klim and c describe the row that is read
+    float s1 = gsrows[(J - 1) * SW + slane];  // S_j[1 + lane]
+    for (int j = J; j >= 1; j--) {
+      // one row ahead (none of this depends on the position)
+      const int4 rpp = j >= 3 ? grows[j - 3] : none;
+      const float s1next = j >= 2 ? gsrows[(j - 2) * SW + slane] : 0.0f;
+      // the stretch of P the walk will read kBtAhead rows from now: the position can only drift
+      // down, by the g's chosen on the way (four lines cover 128 cells)
+      if (lane < 4 && j - 2 - kBtAhead >= 0) prefetch_l2(slab + (j - 2 - kBtAhead) * rowFloats + max(k - 1 - 32 * lane, 0));
+      const int gm = min(rc.y, k);                           // candidates g = 1 .. gm (k-g >= 0)
+      const float* prow = slab + max(j - 2, 0) * rowFloats;  // P[j-1][x] at prow[x-1] (j >= 2)
+      const int klp = rp.z;
+      const float cp = __int_as_float(rp.w);
+      unsigned bestKey = keyFloor;  // best = -10000
+      int sol = 0;
+      for (int g0 = 1; g0 <= gm; g0 += LANES) {
+        const int g = g0 + lane;
+        const int x = k - g;
+        // unconditional loads on clamped, always-valid addresses; the cases are sorted out below
+        const float pv = prow[max(x, 1) - 1];
+        const float sv = g0 == 1 ? s1 : gsrows[(j - 1) * SW + min(g, SW) - 1];
+        const float sg = g <= W - 1 ? sv : 0.0f;  // a g the table does not hold: Go map miss
+        float pg = x <= 0 ? -10000.0f : (x >= klp ? cp : pv);
+        if (j == 1) pg = 0.0f;  // row 0
+        const float p = sg + pg;
+        // strict '>' in increasing g == the first lane holding the maximum; a NaN never wins
+        const unsigned key = (g <= gm && p == p) ? f32_key(p) : 0u;
+        const unsigned top = __reduce_max_sync(full, key);
+        if (top > bestKey) {
+          bestKey = top;
+          sol = g0 + __ffs((int)(__ballot_sync(full, key == top) >> shift)) - 1;
         }
       }
+      if (lane == 0) out[rc.x] = sol;
+      k -= sol;
+      rc = rp;
+      rp = rpp;
+      s1 = s1next;
     }
   }
-  __syncwarp();
-  // ---- phase 2: validateResult (utils.go:18-42) per round; a panic it raises replaces the one in flight
-  for (int q = 0; q < kBtRounds && rr0 + q < count; q++) {
-    const int rr = rr0 + q;
-    const int r = r0 + rr;
-    const int o = a.job_off[r] - a.job_base;
-    const int n = a.job_off[r + 1] - a.job_off[r];
-    const FfdlMeta meta = sc.meta[rr];
-    if (n == 0 || meta.st == VODA_ST_BOUND) {
-      if (lane == 0) a.out_status[r] = n == 0 ? VODA_ST_OK : VODA_ST_BOUND;
-      continue;
-    }
-    int worst = 99;
-    long long sum = 0;
-    for (int base = 0; base < n; base += 32 * 8) {  // 24 loads in flight per lane, then the checks
-      int v[8], mn[8], mx[8];
+  __syncwarp(full);
+  // ---- phase 2: validateResult (utils.go:18-42); a panic it raises replaces the one in flight
+  if (n == 0 || meta.st == VODA_ST_BOUND) {
+    if (lane == 0) a.out_status[r] = n == 0 ? VODA_ST_OK : VODA_ST_BOUND;
+    return;
+  }
+  int worst = 99;
+  long long sum = 0;
+  for (int base = 0; base < n; base += LANES * 8) {  // 24 loads in flight per lane, then the checks
+    int v[8], mn[8], mx[8];
 #pragma unroll
-      for (int u = 0; u < 8; u++) {
-        const int i = base + 32 * u + lane;
-        const bool ok = i < n;
-        v[u] = ok ? a.out_gpus[o + i] : 0;
-        mn[u] = ok ? a.min_proc[o + i] : 0;
-        mx[u] = ok ? a.max_proc[o + i] : 0x7fffffff;
-      }
+    for (int u = 0; u < 8; u++) {
+      const int i = base + LANES * u + lane;
+      const bool ok = i < n;
+      v[u] = ok ? a.out_gpus[o + i] : 0;
+      mn[u] = ok ? a.min_proc[o + i] : 0;
+      mx[u] = ok ? a.max_proc[o + i] : 0x7fffffff;
+    }
 #pragma unroll
-      for (int u = 0; u < 8; u++) {
-        int st = 99;
-        if (v[u] < 0) st = VODA_ST_NEGATIVE;
-        else if (v[u] > 0 && v[u] < mn[u]) st = VODA_ST_LESS_THAN_MIN;
-        else if (v[u] > mx[u]) st = VODA_ST_EXCEEDED_MAX;
-        worst = min(worst, st);
-        sum += v[u];
-      }
+    for (int u = 0; u < 8; u++) {
+      int st = 99;
+      if (v[u] < 0) st = VODA_ST_NEGATIVE;
+      else if (v[u] > 0 && v[u] < mn[u]) st = VODA_ST_LESS_THAN_MIN;
+      else if (v[u] > mx[u]) st = VODA_ST_EXCEEDED_MAX;
+      worst = min(worst, st);
+      sum += v[u];
     }
-    for (int d = 16; d > 0; d >>= 1) {
-      worst = min(worst, __shfl_xor_sync(0xffffffffu, worst, d));
-      sum += __shfl_xor_sync(0xffffffffu, sum, d);
-    }
-    if (lane == 0) {
-      int vv = worst != 99 ? worst : (sum > (long long)meta.K ? VODA_ST_EXCEEDED_TOTAL : VODA_ST_OK);
-      a.out_status[r] = vv ? vv : meta.st;
-    }
+  }
+  for (int d = LANES / 2; d > 0; d >>= 1) {
+    worst = min(worst, __shfl_xor_sync(full, worst, d));
+    sum += __shfl_xor_sync(full, sum, d);
+  }
+  if (lane == 0) {
+    int vv = worst != 99 ? worst : (sum > (long long)meta.K ? VODA_ST_EXCEEDED_TOTAL : VODA_ST_OK);
+    a.out_status[r] = vv ? vv : meta.st;
   }
 }
 
@@ -646,8 +642,19 @@ cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* sc
   ffdl_dp_kernel<<<grid, kThreads, smem, stream>>>(a, r0, count, sc, KTcap, SW, Jp);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  const int perBlock = (kBtThreads / 32) * kBtRounds;  // rounds per block: eight lanes per round
-  ffdl_backtrack_kernel<<<(count + perBlock - 1) / perBlock, kBtThreads, 0, stream>>>(a, r0, count, sc);
+  // a warp per round while all the walks are resident at once, two or four rounds per warp beyond
+  int btPerSm = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&btPerSm, ffdl_backtrack_kernel<32>, kBtThreads, 0);
+  if (e != cudaSuccess) return e;
+  const int warps = kBtThreads / 32;
+  const long long resident = (long long)sms * btPerSm * warps;
+  auto blocks = [&](int perWarp) { return (count + warps * perWarp - 1) / (warps * perWarp); };
+  if (count <= resident)
+    ffdl_backtrack_kernel<32><<<blocks(1), kBtThreads, 0, stream>>>(a, r0, count, sc);
+  else if (count <= 2 * resident)
+    ffdl_backtrack_kernel<16><<<blocks(2), kBtThreads, 0, stream>>>(a, r0, count, sc);
+  else
+    ffdl_backtrack_kernel<8><<<blocks(4), kBtThreads, 0, stream>>>(a, r0, count, sc);
   return cudaGetLastError();
 }
 
