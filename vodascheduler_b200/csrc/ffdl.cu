@@ -1,15 +1,18 @@
 // ffdl.cu — FfDLOptimizer.Schedule (pkg/algorithm/ffdl_optimizer.go:32-130) for a batch of
 // rounds, hand-written for sm_100a.
 //
-// One CTA owns one round at a time (persistent grid striding over rounds).  Per round:
-//   1. stable sort of the jobs by SubmitTime (:45-47)            -> block bitonic argsort
+// One WARP (a 32-thread CTA) owns one round at a time (persistent grid striding over rounds).
+// Per round:
+//   1. stable sort of the jobs by SubmitTime (:45-47)            -> bitonic argsort
 //   2. trim to the first J = min(n, K) jobs (:54-65)
 //   3. DP  P[j][k] = max_g S_j[g] + P[j-1][k-g], g in [1, max_j], k-g >= 0, rows initialised
-//      to -10000 (:78-105) -> ONE ROW PER CTA STEP: rows j-1 and j live in shared memory
-//      (float4 groups), each thread owns kCells adjacent cells and slides a register window
-//      of row j-1 over g, so a block of 4 g-steps costs one LDS.128 of P and one LDS.128
-//      (broadcast) of S for 4*kCells add+max pairs.  The forward pass keeps ONLY the values:
-//      per candidate it is one FADD and half a three-input FMNMX3.
+//      to -10000 (:78-105) -> ONE ROW PER STEP, IN PLACE: the row lives in shared memory
+//      (float4 groups); a cell only reads cells to its left, so the warp takes the row's tiles
+//      from the right end, 32 at a time, every lane reading its window of row j-1 before row j
+//      lands on it (a __syncwarp, no CTA barrier anywhere in the row loop).  A lane owns 8
+//      adjacent cells and slides a three-group register window of row j-1 over g, so a block of
+//      4 g-steps costs one LDS.128 of P for 32 add+max pairs.  The forward pass keeps ONLY the
+//      values: per candidate it is one FADD and half a three-input FMNMX3.
 //   4. The reference also records SOL[j][k] = the g that won (strict '>', so the smallest g
 //      among equals).  Tracking it costs two more instructions per candidate on the pipe that
 //      already bounds the loop, and only J of the J*K entries are ever read.  Instead the rows
@@ -41,13 +44,12 @@ namespace voda {
 
 namespace {
 
-#ifndef VODA_FFDL_THREADS
-#define VODA_FFDL_THREADS 64
-#endif
 #ifndef VODA_FFDL_MINBLOCKS
-#define VODA_FFDL_MINBLOCKS 12
+#define VODA_FFDL_MINBLOCKS 20
 #endif
-constexpr int kThreads = VODA_FFDL_THREADS;
+// One warp per round: the row loop needs no CTA barrier, and the warp updates ONE row buffer in
+// place (tiles are taken from the right end of the band: a cell only reads cells to its left).
+constexpr int kThreads = 32;
 constexpr int kCells = 8;  // adjacent cells per thread: two float4 groups, a three-group window
 
 // Per-row constants, worked out once per round after the sort and read back with one LDS.64
@@ -61,11 +63,10 @@ __device__ __forceinline__ unsigned long long pack_row(int nblk, bool slow, int 
          ((unsigned long long)(unsigned)tcE << 32) | ((unsigned long long)(unsigned)fillE << 48);
 }
 
-// Shared memory per CTA: two row buffers and 20 bytes per job; the sort keys' space is reused
+// Shared memory per CTA: one row buffer and 20 bytes per job; the sort keys' space is reused
 // for the row constants once the sort is done.
 struct FfdlSmem {
-  float4* rowA;    // row buffers (see Row below); the pointer is E[0]
-  float4* rowB;
+  float4* row;     // the row buffer (see below); the pointer is E[0]
   int64_t* khi;    // [Jp]  sort key (seconds); after the sort: the packed row constants
   int32_t* klo;    // [Jp]  sort key (nanoseconds); after the sort: srmax, max over the row's usable g of S_j[g]
   int* perm;       // [Jp]  sorted position -> job; then smaxc = clamp(max_proc, 0, K) in sorted order
@@ -130,12 +131,14 @@ __device__ __forceinline__ void ffdl_block8(float (&best)[8], const float4 sq, c
   }
 }
 
-__device__ __forceinline__ void ffdl_store_tile(float4* __restrict__ cur, int ost, int tq, const float (&best)[8],
-                                                float4* __restrict__ grow) {
+__device__ __forceinline__ void ffdl_store_tile(float4* row, int ost, int tq, const float (&best)[8],
+                                                float4* __restrict__ grow, bool act) {
   const float4 lo = make_float4(best[0], best[1], best[2], best[3]);
   const float4 hi = make_float4(best[4], best[5], best[6], best[7]);
-  cur[tq + ost] = lo;  // group 2tq+1
-  cur[tq + 1] = hi;    // group 2tq+2
+  __syncwarp();  // every lane of the pass has read its window of row j-1 before row j lands on it
+  if (!act) return;
+  row[tq + ost] = lo;  // group 2tq+1
+  row[tq + 1] = hi;    // group 2tq+2
   if (grow) {  // the slab row is in cell order; streamed: nothing reads it before the backtrack kernel
     __stcs(grow + 2 * tq, lo);
     __stcs(grow + 2 * tq + 1, hi);
@@ -147,46 +150,46 @@ __device__ __forceinline__ void ffdl_store_tile(float4* __restrict__ cur, int os
 // For the block of g = 4m+1 .. 4m+4 the cells need P[base-3 .. base+8], base = 8*tq - 4m, i.e.
 // groups q0 .. q0+2 with q0 = 2*tq - m.
 template <int NB>
-__device__ __forceinline__ void ffdl_tile_nb(const float4* __restrict__ prev, float4* __restrict__ cur, int ost,
-                                             int tq, const float4 sA, const float4 sB, float4* __restrict__ grow) {
+__device__ __forceinline__ void ffdl_tile_nb(float4* row, int ost, int tq, const float4 sA,
+                                             const float4 sB, float4* __restrict__ grow, bool act) {
   float best[8];
 #pragma unroll
   for (int c = 0; c < 8; c++) best[c] = -10000.0f;
-  const float4 g0 = prev[tq], g1 = prev[tq + ost], g2 = prev[tq + 1];
+  const float4 g0 = row[tq], g1 = row[tq + ost], g2 = row[tq + 1];
   ffdl_block8(best, sA, g0, g1, g2);
   if (NB >= 2) {
-    const float4 gm = prev[tq - 1 + ost];
+    const float4 gm = row[tq - 1 + ost];
     ffdl_block8(best, sB, gm, g0, g1);
   }
-  ffdl_store_tile(cur, ost, tq, best, grow);
+  ffdl_store_tile(row, ost, tq, best, grow, act);
 }
 
 // The general tile: any number of blocks (S read from the round's sorted S rows in global
 // memory), then the candidates g in [gslow0, gslow1] the dense table does not hold (the Go map
 // misses, S = 0; rare: max_j >= W).
-__device__ __forceinline__ void ffdl_tile_any(const float4* __restrict__ prev, float4* __restrict__ cur, int ost,
-                                              int tq, const float4* __restrict__ s4, int nblk, int gslow0,
-                                              int gslow1, float4* __restrict__ grow) {
+__device__ __forceinline__ void ffdl_tile_any(float4* row, int ost, int tq,
+                                              const float4* __restrict__ s4, int nblk, int gslow0, int gslow1,
+                                              float4* __restrict__ grow, bool act) {
   float best[8];
 #pragma unroll
   for (int c = 0; c < 8; c++) best[c] = -10000.0f;
   const int qtop = 2 * tq;
   // the window is three groups; instead of shifting registers after every block the three
   // roles rotate through three unrolled copies of the block
-  float4 g0 = *grp(prev, ost, qtop), g1 = *grp(prev, ost, qtop + 1), g2 = *grp(prev, ost, qtop + 2);
+  float4 g0 = *grp(row, ost, qtop), g1 = *grp(row, ost, qtop + 1), g2 = *grp(row, ost, qtop + 2);
   int m = 0;
   for (; m + 3 <= nblk; m += 3) {
     ffdl_block8(best, s4[m], g0, g1, g2);
-    g2 = *grp(prev, ost, qtop - m - 1);
+    g2 = *grp(row, ost, qtop - m - 1);
     ffdl_block8(best, s4[m + 1], g2, g0, g1);
-    g1 = *grp(prev, ost, qtop - m - 2);
+    g1 = *grp(row, ost, qtop - m - 2);
     ffdl_block8(best, s4[m + 2], g1, g2, g0);
-    g0 = *grp(prev, ost, qtop - m - 3);
+    g0 = *grp(row, ost, qtop - m - 3);
   }
   if (m < nblk) {
     ffdl_block8(best, s4[m], g0, g1, g2);
     if (m + 1 < nblk) {
-      g2 = *grp(prev, ost, qtop - m - 1);
+      g2 = *grp(row, ost, qtop - m - 1);
       ffdl_block8(best, s4[m + 1], g2, g0, g1);
     }
   }
@@ -194,10 +197,10 @@ __device__ __forceinline__ void ffdl_tile_any(const float4* __restrict__ prev, f
 #pragma unroll
     for (int c = 0; c < 8; c++) {
       const int k = 8 * tq + 1 + c;
-      for (int g = gslow0; g <= gslow1 && g <= k; g++) best[c] = fmaxf(best[c], 0.0f + cell(prev, ost, k - g));
+      for (int g = gslow0; g <= gslow1 && g <= k; g++) best[c] = fmaxf(best[c], 0.0f + cell(row, ost, k - g));
     }
   }
-  ffdl_store_tile(cur, ost, tq, best, grow);
+  ffdl_store_tile(row, ost, tq, best, grow, act);
 }
 
 // 16-byte asynchronous copy global -> shared (LDGSTS)
@@ -296,12 +299,11 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT,
                           float* __restrict__ slab, size_t rowFloats, const float* gs, FfdlRow* grows,
                           const float4** last) {
   const int tid = threadIdx.x;
-  float4* prev = sm.rowA;
-  float4* cur = sm.rowB;
+  float4* row = sm.row;
   // row 0: P[0][k] = 0 for every k (:80-82)
   for (int i = tid; i <= KT; i += kThreads) {
-    prev[i] = i == 0 ? make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, 0.0f) : make_float4(0.f, 0.f, 0.f, 0.f);
-    prev[i + ost] = make_float4(0.f, 0.f, 0.f, 0.f);
+    row[i] = i == 0 ? make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, 0.0f) : make_float4(0.f, 0.f, 0.f, 0.f);
+    row[i + ost] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   const unsigned long long* rowq = reinterpret_cast<const unsigned long long*>(sm.khi);
   const float* srmax = reinterpret_cast<const float*>(sm.klo);
@@ -343,31 +345,30 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT,
     const float ccur = fmaxf(-10000.0f, srmax[j - 1] + cprev);
     if (tid == 0) gr->c = ccur;
     float4* gdst = j < J ? grow : nullptr;  // row J is only read at [K], from shared memory
-    if (!slow && nblk == 1) {
-      for (int tq = tc0 + tid; tq < tcE; tq += kThreads) ffdl_tile_nb<1>(prev, cur, ost, tq, sA, sBv, gdst);
-    } else if (!slow && nblk == 2) {
-      for (int tq = tc0 + tid; tq < tcE; tq += kThreads) ffdl_tile_nb<2>(prev, cur, ost, tq, sA, sBv, gdst);
-    } else {
-      const int gslow1 = slow ? gr->gmax : -1;  // written by this CTA before the last barrier
-      for (int tq = tc0 + tid; tq < tcE; tq += kThreads)
-        ffdl_tile_any(prev, cur, ost, tq, s4, nblk, gslow0, gslow1, gdst);
-    }
+    // passes of 32 tiles from the right end of the band; lanes beyond the band recompute its last
+    // tile and store nothing (every lane must reach the __syncwarp in front of the stores)
     {
       const float4 c4 = make_float4(ccur, ccur, ccur, ccur);
-      for (int tq = tcE + tid; tq < fillE; tq += kThreads) {
-        cur[tq + ost] = c4;
-        cur[tq + 1] = c4;
+      for (int tq = tcE + tid; tq < fillE; tq += kThreads) {  // not read by this row's tiles
+        row[tq + ost] = c4;
+        row[tq + 1] = c4;
       }
     }
+    const int gslow1 = slow ? gr->gmax : -1;  // written by this warp during the set-up
+    for (int base = tc0 + ((tcE - tc0 - 1) & ~31); base >= tc0 && tcE > tc0; base -= 32) {
+      const bool act = base + tid < tcE;
+      const int tq = min(base + tid, tcE - 1);
+      if (!slow && nblk == 1) ffdl_tile_nb<1>(row, ost, tq, sA, sBv, gdst, act);
+      else if (!slow && nblk == 2) ffdl_tile_nb<2>(row, ost, tq, sA, sBv, gdst, act);
+      else ffdl_tile_any(row, ost, tq, s4, nblk, gslow0, gslow1, gdst, act);
+    }
+    __syncwarp();
     cprev = ccur;
-    if (tid == 0) cur[0] = make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, -10000.0f);  // P[j][0]
+    if (tid == 0) row[0] = make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, -10000.0f);  // P[j][0]
     cp_async_wait<1>();  // everything but this row's stage_s has landed: the next row's S is in its slot
     __syncthreads();
-    float4* t = prev;
-    prev = cur;
-    cur = t;
   }
-  *last = prev;
+  *last = row;
 }
 
 // Kernel A: sort + DP rows.  One CTA per round at a time; P rows / row records / meta go to the
@@ -379,8 +380,7 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
   {
     unsigned char* p = smem_raw;
     const int ph = pad_half(SW);
-    sm.rowA = reinterpret_cast<float4*>(p) + ph; p += sizeof(float4) * (size_t)row_groups(SW, KTcap);
-    sm.rowB = reinterpret_cast<float4*>(p) + ph; p += sizeof(float4) * (size_t)row_groups(SW, KTcap);
+    sm.row = reinterpret_cast<float4*>(p) + ph; p += sizeof(float4) * (size_t)row_groups(SW, KTcap);
     sm.sring = reinterpret_cast<float4*>(p); p += sizeof(float) * 4 * (size_t)SW;
     sm.khi = reinterpret_cast<int64_t*>(p); p += sizeof(int64_t) * (size_t)Jp;
     sm.klo = reinterpret_cast<int32_t*>(p); p += sizeof(int32_t) * (size_t)Jp;
@@ -391,10 +391,8 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
   const int ost = pad_half(SW) + KTcap + 1;  // O[i] = E[i + ost]
   for (int q = tid; q < pad_half(SW); q += kThreads) {  // written once: nothing else stores there
     const float4 ninf = make_float4(VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF, VODA_NEG_INF);
-    sm.rowA[-1 - q] = ninf;
-    sm.rowA[-1 - q + ost] = ninf;
-    sm.rowB[-1 - q] = ninf;
-    sm.rowB[-1 - q + ost] = ninf;
+    sm.row[-1 - q] = ninf;
+    sm.row[-1 - q + ost] = ninf;
   }
 
   for (int rr = blockIdx.x; rr < count; rr += gridDim.x) {
@@ -585,7 +583,7 @@ static void ffdl_shape(const AllocArgs& a, int* KTcap, int* SW, int* Jp, size_t*
   if (sw < 1) sw = 1;
   *SW = (sw + 3) & ~3;
   *Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  *smem = sizeof(float4) * 2 * (size_t)row_groups(*SW, *KTcap) + sizeof(float) * 4 * (size_t)(*SW) +
+  *smem = sizeof(float4) * (size_t)row_groups(*SW, *KTcap) + sizeof(float) * 4 * (size_t)(*SW) +
           (sizeof(int64_t) + 3 * sizeof(int32_t)) * (size_t)(*Jp);
 }
 
