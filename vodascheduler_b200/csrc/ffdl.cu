@@ -51,6 +51,15 @@ namespace {
 // place (tiles are taken from the right end of the band: a cell only reads cells to its left).
 constexpr int kThreads = 32;
 constexpr int kCells = 8;  // adjacent cells per thread: two float4 groups, a three-group window
+// Checkpointing: when no job of the round can take more than kCkptGmax GPUs (the usual case:
+// the speedup tables stop at 32), only every kCkpt-th row of P is stored, and the backtrack
+// recomputes the rows in between on the narrow band its walk can reach (kCkpt * kCkptGmax
+// cells at most).  That cuts the scratch traffic, the DP kernel's main memory cost, by kCkpt.
+constexpr int kCkpt = 4;
+constexpr int kCkptGmax = 32;
+constexpr int kBand = kCkpt * kCkptGmax;  // cells per band row
+constexpr int kBandPad = kCkptGmax;       // -inf cells in front of a band row (columns below 0)
+constexpr int kBandRow = kBandPad + kBand + 32;
 
 // Per-row constants, worked out once per round after the sort and read back with one LDS.64
 // and one LDS.32 per row: four 16-bit fields packed in a word, and the row maximum.
@@ -79,7 +88,7 @@ struct FfdlMeta {
   int32_t J;   // rows of the DP (jobs kept after the trim)
   int32_t st;  // VODA_ST_OK, or the panic raised before / by the DP
   int32_t K;
-  int32_t pad;
+  int32_t sparse;  // 1: only every kCkpt-th row of P was stored (see the backtrack kernel)
 };
 // ... and per DP row j (1-based; record j-1), 16 bytes so that one load fetches it
 struct __align__(16) FfdlRow {
@@ -215,7 +224,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // Everything the row loop and the backtrack need to know about the rows of one round, worked
 // out once after the sort: the sorted S rows (to scratch), the row maxima, the two running
 // sums behind the trims, the tile ranges.
-__device__ void ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, int K, int KT, int SW,
+__device__ bool ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, int K, int KT, int SW,
                                 float* gs, FfdlRow* grows) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int W = a.stride;
@@ -226,11 +235,13 @@ __device__ void ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, i
   // a. a thread per row.  First the row's size limit (one dependent load per row, all rows of
   //    the thread in flight together), then S_j[1..] with -inf beyond the row's table limit:
   //    only the entries the row can use are read.
+  int gtop = 0;
 #pragma unroll 4
   for (int j = tid; j < J; j += kThreads) {
     const int pj = sm.perm[j];
     const int gmax = min(a.max_proc[o + pj], K);
     smaxc[j] = max(0, gmax);
+    gtop = max(gtop, gmax);
     grows[j].job = pj;
     grows[j].gmax = gmax;
   }
@@ -292,10 +303,11 @@ __device__ void ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, i
     grows[j].klim = klim;
   }
   __syncthreads();
+  return __reduce_max_sync(0xffffffffu, gtop) <= kCkptGmax;  // kThreads == 32
 }
 
 // All DP rows of one round.  Returns with the last row in `*last` (shared memory).
-__device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT, int SW, int ost,
+__device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT, int SW, int ost, bool sparse,
                           float* __restrict__ slab, size_t rowFloats, const float* gs, FfdlRow* grows,
                           const float4** last) {
   const int tid = threadIdx.x;
@@ -344,7 +356,8 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT,
     // is monotone, so the maximum commutes with the addition exactly
     const float ccur = fmaxf(-10000.0f, srmax[j - 1] + cprev);
     if (tid == 0) gr->c = ccur;
-    float4* gdst = j < J ? grow : nullptr;  // row J is only read at [K], from shared memory
+    // row J is only read at [K], from shared memory; a sparse round stores every kCkpt-th row
+    float4* gdst = (j < J && (!sparse || j % kCkpt == 0)) ? grow : nullptr;
     // passes of 32 tiles from the right end of the band; lanes beyond the band recompute its last
     // tile and store nothing (every lane must reach the __syncwarp in front of the stores)
     {
@@ -429,11 +442,12 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
     const int KT = (K + kCells - 1) / kCells;
     float* gs = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)SW;
     FfdlRow* grows = sc.rows + (size_t)rr * (size_t)sc.Jcap;
-    ffdl_setup_rows(a, sm, o, J, K, KT, SW, gs, grows);
+    const bool sparse = ffdl_setup_rows(a, sm, o, J, K, KT, SW, gs, grows);
     const float4* last = nullptr;
-    ffdl_rows(a, sm, J, KT, SW, ost, sc.P + (size_t)rr * sc.slabFloats, sc.rowFloats, gs, grows, &last);
+    ffdl_rows(a, sm, J, KT, SW, ost, sparse, sc.P + (size_t)rr * sc.slabFloats, sc.rowFloats, gs, grows, &last);
     const float PJK = cell(last, ost, K);
     meta.J = J;
+    meta.sparse = sparse ? 1 : 0;
     if (PJK <= 0.0f) meta.st = VODA_ST_INFEASIBLE;  // :109-114 (NaN is not <= 0, as in Go)
     if (tid == 0) sc.meta[rr] = meta;
   }
@@ -465,24 +479,145 @@ __device__ __forceinline__ unsigned f32_key(float p) {
   return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
 }
 
-// LANES lanes walk one round: 32 (a warp per round, the shortest chain) while every round of
-// the launch fits on the GPU at once, 16 or 8 (two or four rounds per warp, whose walks diverge)
-// beyond.
-template <int LANES>
+// The walk of a SPARSE round (only every kCkpt-th row of P in scratch): in segments of kCkpt
+// rows.  For the segment of walk rows jTop .. c+1 (c the checkpoint row below) the warp loads
+// the stretch of row c its walk can reach — the position only drifts down, by at most the row's
+// g limit per step, so row r is needed on [k - D_r, k-1], D_r = the later rows' limits summed,
+// 128 cells at most — recomputes rows c+1 .. jTop-1 on their (shrinking) stretches into shared
+// memory with the forward pass's own recurrence (same additions, a maximum: any order gives the
+// same value), and then takes the kCkpt walk steps from shared memory.  One dependent global
+// load per segment instead of one per row.
+__device__ __forceinline__ void ffdl_walk_sparse(const AllocArgs& a, const FfdlScratch& sc, int rr, int o, int J, int K,
+                                                 int lane, float (*band)[kBandRow], float (*ssm)[32]) {
+  const unsigned full = 0xffffffffu;
+  const float* slab = sc.P + (size_t)rr * sc.slabFloats;
+  const float* gsrows = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)sc.SW;
+  const int4* grows = reinterpret_cast<const int4*>(sc.rows + (size_t)rr * (size_t)sc.Jcap);  // job, gmax, klim, c
+  int32_t* out = a.out_gpus + o;
+  const int SW = sc.SW;
+  const int W = a.stride;
+  const int rowFloats = (int)sc.rowFloats;
+  const int slane = min(lane, SW - 1);
+  const int4 none = make_int4(0, 0, 0, 0);
+  const unsigned keyFloor = f32_key(-10000.0f);
+  int k = K;
+  for (int jTop = J; jTop >= 1;) {
+    const int c = ((jTop - 1) / kCkpt) * kCkpt;  // rows c .. jTop-1 feed the walk rows jTop .. c+1
+    const int nr = jTop - c;                     // 1 .. kCkpt
+    int4 rec[kCkpt];    // rec[i]: row c+1+i
+    float sreg[kCkpt];  // S_{c+1+i}[1 + lane]
+    const int4* recp = grows + c;
+    const float* sp = gsrows + c * SW + slane;
+#pragma unroll
+    for (int i = 0; i < kCkpt; i++) {  // (past the segment the loads stay inside the scratch and are masked)
+      rec[i] = recp[i];
+      sreg[i] = sp[i * SW];
+    }
+    const int4 recc = c >= 1 ? recp[-1] : none;  // the checkpoint row's klim and c
+    // the next segment's records and S rows do not depend on the position: pull them into L2
+    if (c >= kCkpt) {
+      if (lane == 0) prefetch_l2(recp - kCkpt - 1);
+      if (lane >= 1 && lane <= kCkpt) prefetch_l2(gsrows + (c - kCkpt + lane - 1) * SW);
+      // ... and so is the stretch of the next checkpoint row just below the current position
+      if (lane >= 8 && lane < 12 && c > kCkpt)
+        prefetch_l2(slab + (c - kCkpt - 1) * rowFloats + max(k - 1 - 32 * (lane - 8), 0));
+    }
+#pragma unroll
+    for (int i = 0; i < kCkpt; i++) {
+      if (i >= nr) rec[i].y = 0;
+      // S as the recurrence uses it: a g the table does not hold reads 0 (a Go map miss)
+      sreg[i] = lane + 1 <= W - 1 ? sreg[i] : 0.0f;
+      ssm[i][lane] = sreg[i];
+    }
+    int lo[kCkpt];  // lo[i]: lowest column of row c+i the walk can read
+    {
+      int D = 0;
+#pragma unroll
+      for (int i = kCkpt - 1; i >= 0; i--) {
+        D += max(0, rec[i].y);  // (0 past the segment)
+        lo[i] = max(0, k - D);
+      }
+    }
+    const int base = lo[0];
+    const int width = k - base;  // <= kBand: columns base .. k-1
+    // 1. the stored row c (or row 0 = 0)
+    {
+      const float* crow = slab + max(c - 1, 0) * rowFloats;  // P[c][x] at crow[x-1]
+      const float cC = __int_as_float(recc.w);
+      for (int idx = lane; idx < width; idx += 32) {
+        const int x = base + idx;
+        const float pv = crow[max(x, 1) - 1];
+        band[0][kBandPad + idx] = c == 0 ? 0.0f : (x == 0 ? -10000.0f : (x >= recc.z ? cC : pv));
+      }
+    }
+    __syncwarp();
+    // 2. rows c+1 .. jTop-1
+#pragma unroll
+    for (int i = 1; i < kCkpt; i++) {
+      if (i < nr) {
+        const int gmax = rec[i - 1].y, klim = rec[i - 1].z;
+        const float cR = __int_as_float(rec[i - 1].w);
+        const float* sv = ssm[i - 1];
+        for (int idx0 = lo[i] - base; idx0 < width; idx0 += 32) {  // uniform trip count
+          const int idx = idx0 + lane;
+          const int x = base + idx;
+          // P[r-1][x-g] sits at prow[-g]; a column below 0 falls into the -inf pad (the stretch
+          // starts at column 0 whenever that can happen), so the k-g >= 0 test needs no branch
+          const float* prow = band[i - 1] + kBandPad + min(idx, width);
+          float best = -10000.0f;
+          int g = 1;
+          for (; g + 1 <= gmax; g += 2) best = fmaxf(fmaxf(best, sv[g - 1] + prow[-g]), sv[g] + prow[-g - 1]);
+          if (g <= gmax) best = fmaxf(best, sv[g - 1] + prow[-g]);
+          if (x == 0) best = -10000.0f;
+          else if (x >= klim) best = cR;
+          if (idx < width) band[i][kBandPad + idx] = best;
+        }
+        __syncwarp();
+      }
+    }
+    // 3. the walk steps jTop .. c+1 (row c+1+i reads band row i)
+#pragma unroll
+    for (int i = kCkpt - 1; i >= 0; i--) {
+      if (i < nr) {
+        const int gm = min(rec[i].y, k);  // candidates g = 1 .. gm (k-g >= 0); gm <= 32 in a sparse round
+        const int g = 1 + lane;
+        const float sg = sreg[i];
+        const float pg = g <= gm ? band[i][kBandPad + k - g - base] : 0.0f;
+        const float p = sg + pg;
+        const unsigned key = (g <= gm && p == p) ? f32_key(p) : 0u;
+        const unsigned top = __reduce_max_sync(full, key);
+        const int sol = top > keyFloor ? __ffs((int)__ballot_sync(full, key == top)) : 0;
+        if (lane == 0) out[rec[i].x] = sol;
+        k -= sol;
+      }
+    }
+    __syncwarp();
+    jTop = c;
+  }
+}
+
 __global__ void __launch_bounds__(kBtThreads)
     ffdl_backtrack_kernel(AllocArgs a, int r0, int count, FfdlScratch sc) {
+  __shared__ float band[kBtThreads / 32][kCkpt][kBandRow];
+  __shared__ float ssm[kBtThreads / 32][kCkpt][32];
+  for (int i = threadIdx.x; i < (kBtThreads / 32) * kCkpt * kBandPad; i += kBtThreads)  // the pads, written once
+    band[i / (kCkpt * kBandPad)][(i / kBandPad) % kCkpt][i % kBandPad] = VODA_NEG_INF;
+  __syncthreads();
+  constexpr int LANES = 32;
   const int wlane = threadIdx.x & 31;
-  const int lane = wlane & (LANES - 1);       // lane within the round's group
-  const int shift = wlane & ~(LANES - 1);     // first lane of the group
-  const unsigned full = LANES == 32 ? 0xffffffffu : (((1u << (LANES & 31)) - 1u) << shift);
-  const int rr = (blockIdx.x * (kBtThreads / 32) + (threadIdx.x >> 5)) * (32 / LANES) + wlane / LANES;
+  const int lane = wlane;
+  const int shift = 0;
+  const unsigned full = 0xffffffffu;
+  const int rr = blockIdx.x * (kBtThreads / 32) + (threadIdx.x >> 5);
   if (rr >= count) return;
   const int r = r0 + rr;
   const int o = a.job_off[r] - a.job_base;
   const int n = a.job_off[r + 1] - a.job_off[r];
   const FfdlMeta meta = sc.meta[rr];
   // ---- phase 1: the walk
-  if (meta.st == VODA_ST_OK && meta.J > 0) {
+  if (meta.st == VODA_ST_OK && meta.J > 0 && meta.sparse) {
+    ffdl_walk_sparse(a, sc, rr, o, meta.J, meta.K, lane, band[threadIdx.x >> 5], ssm[threadIdx.x >> 5]);
+  } else if (meta.st == VODA_ST_OK && meta.J > 0) {
     const float* slab = sc.P + (size_t)rr * sc.slabFloats;
     const float* gsrows = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)sc.SW;
     const int4* grows = reinterpret_cast<const int4*>(sc.rows + (size_t)rr * (size_t)sc.Jcap);  // job, gmax, klim, c
@@ -640,19 +775,8 @@ cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* sc
   ffdl_dp_kernel<<<grid, kThreads, smem, stream>>>(a, r0, count, sc, KTcap, SW, Jp);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
-  // a warp per round while all the walks are resident at once, two or four rounds per warp beyond
-  int btPerSm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&btPerSm, ffdl_backtrack_kernel<32>, kBtThreads, 0);
-  if (e != cudaSuccess) return e;
-  const int warps = kBtThreads / 32;
-  const long long resident = (long long)sms * btPerSm * warps;
-  auto blocks = [&](int perWarp) { return (count + warps * perWarp - 1) / (warps * perWarp); };
-  if (count <= resident)
-    ffdl_backtrack_kernel<32><<<blocks(1), kBtThreads, 0, stream>>>(a, r0, count, sc);
-  else if (count <= 2 * resident)
-    ffdl_backtrack_kernel<16><<<blocks(2), kBtThreads, 0, stream>>>(a, r0, count, sc);
-  else
-    ffdl_backtrack_kernel<8><<<blocks(4), kBtThreads, 0, stream>>>(a, r0, count, sc);
+  const int warps = kBtThreads / 32;  // a warp per round
+  ffdl_backtrack_kernel<<<(count + warps - 1) / warps, kBtThreads, 0, stream>>>(a, r0, count, sc);
   return cudaGetLastError();
 }
 
