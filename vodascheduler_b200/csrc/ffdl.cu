@@ -596,7 +596,10 @@ __device__ __forceinline__ void ffdl_walk_sparse(const AllocArgs& a, const FfdlS
   }
 }
 
-__global__ void __launch_bounds__(kBtThreads)
+#ifndef VODA_BT_MINBLOCKS
+#define VODA_BT_MINBLOCKS 8
+#endif
+__global__ void __launch_bounds__(kBtThreads, VODA_BT_MINBLOCKS)
     ffdl_backtrack_kernel(AllocArgs a, int r0, int count, FfdlScratch sc) {
   __shared__ float band[kBtThreads / 32][kCkpt][kBandRow];
   __shared__ float ssm[kBtThreads / 32][kCkpt][32];
