@@ -118,11 +118,42 @@ def test_esrjf_large_rounds(ctx, oracle):
 
 
 def test_ffdl_wide_max_and_table_edge(ctx, oracle):
-    """max_proc beyond the dense table (map miss => S = 0) and beyond 255 (uint16 SOL path)."""
+    """max_proc beyond the dense table (map miss => S = 0) and far beyond 32 (every row of P
+    stored, row-by-row backtrack)."""
     b = synth.jobs_batch("FfDLOptimizer", rounds=12, jobs_per_round=24, total_gpu=700)
     b.max_proc = (b.max_proc.astype(np.int64) * np.where(np.arange(b.jobs) % 5 == 0, 40, 2)).astype(np.int32)
     _same(ctx, oracle, b)
     b.total_gpu[:] = 90
+    _same(ctx, oracle, b)
+
+
+@pytest.mark.parametrize("gcap", [31, 32, 33, 34])
+@pytest.mark.parametrize("jobs", [1, 2, 3, 4, 5, 7, 8, 9, 63, 64, 65])
+def test_ffdl_checkpoint_boundaries(ctx, oracle, gcap, jobs):
+    """The backtrack walks a round in segments of 4 rows from every 4th stored row of P when no job
+    can take more than 32 GPUs, and row by row from every row otherwise: both sides of that
+    switch, every remainder of the row count modulo 4, budgets from 0 to far beyond the demand."""
+    b = synth.jobs_batch("FfDLOptimizer", rounds=24, jobs_per_round=jobs, total_gpu=96, ragged=False)
+    b.max_proc = np.minimum(b.max_proc * 4, gcap).astype(np.int32)
+    b.max_proc[::3] = gcap  # the widest job sits in every round
+    b.total_gpu[:] = np.resize(np.array([0, 1, 2, 3, 5, 31, 32, 33, 64, 97, 130, 1000], np.int32), b.rounds)
+    _same(ctx, oracle, b)
+
+
+def test_ffdl_ties_and_flat_tables(ctx, oracle):
+    """Flat, zero, negative and NaN-free degenerate speedup tables make most candidates tie: the
+    strict '>' keeps the smallest g in the reference, and so must the re-evaluated arg-max."""
+    b = synth.jobs_batch("FfDLOptimizer", rounds=40, jobs_per_round=37, total_gpu=150)
+    S = b.speedup.reshape(b.jobs, b.speedup_stride).copy()
+    kind = np.arange(b.jobs) % 5
+    S[kind == 0, 1:] = 1.0                      # flat
+    S[kind == 1, :] = 0.0                       # all zero (also +0 vs -0 below)
+    S[kind == 2, 1::2] = -0.0
+    S[kind == 3, 1:] = -np.abs(S[kind == 3, 1:])  # negative: -10000 init never loses to them
+    S[kind == 4, 1:] = np.round(S[kind == 4, 1:])  # coarse values: many equal sums
+    b.speedup = S.reshape(-1).astype(np.float32)
+    _same(ctx, oracle, b)
+    b.total_gpu[:] = 17
     _same(ctx, oracle, b)
 
 
