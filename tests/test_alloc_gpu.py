@@ -110,6 +110,26 @@ def test_tiresias_c1_shape(ctx, oracle):
     assert (g.reshape(400, 64).sum(1) <= 16).all()
 
 
+@pytest.mark.parametrize("algo", ["Tiresias", "ElasticTiresias"])
+def test_tiresias_times_outside_the_packed_key(ctx, oracle, algo):
+    """The queue sort packs (queue, FirstStartTime) into 64 bits when every key of the round fits
+    (seconds in [0, 2^32-1), or the MaxTime sentinel); rounds with anything else — times before
+    1970, beyond 2106, the sentinel's seconds with other nanoseconds — take the general compare.
+    Both kinds of round in one batch, ties included."""
+    b = synth.jobs_batch(algo, rounds=96, jobs_per_round=64, total_gpu=16)
+    sec = b.first_sec.copy()
+    ns = b.first_nsec.copy()
+    rnd = np.repeat(np.arange(b.rounds), 64)
+    j = np.arange(b.jobs) % 64
+    sec[(rnd % 4 == 1) & (j % 7 == 0)] = -5                       # before the epoch
+    sec[(rnd % 4 == 2) & (j % 5 == 0)] = (1 << 32) + 17           # beyond the 32-bit field
+    ns[(rnd % 4 == 3) & (j % 3 == 0) & (sec == synth.MAXTIME_SEC)] = 5  # sentinel seconds, other nanoseconds
+    sec[(rnd % 8 == 0) & (j % 2 == 0)] = 1_790_000_000            # packable rounds with heavy ties
+    ns[(rnd % 8 == 0) & (j % 2 == 0)] = 7
+    b.first_sec, b.first_nsec = sec, ns.astype(b.first_nsec.dtype)
+    _same(ctx, oracle, b)
+
+
 def test_esrjf_large_rounds(ctx, oracle):
     """The policy of BASELINE config 4 at 1024 jobs per round (bitonic sort + epoch fill)."""
     for algo in ("ElasticSRJF", "ElasticFIFO"):

@@ -28,6 +28,8 @@ namespace {
 
 constexpr int kThreads = 128;     // upper bound; rounds of <= 64 jobs run with 64 threads
 constexpr int kRankSortMax = 96;  // rounds up to this size use the rank sort
+constexpr long long kMaxTimeSec = 0x7fffffffffffffffll - 62135596800ll;  // types.MaxTime (types.go:65)
+constexpr int kMaxTimeNsec = 999999999;
 
 struct TirSmem {
   int64_t* khi;
@@ -35,6 +37,7 @@ struct TirSmem {
   int32_t* klo;
   int32_t* kq;     // queue index (Q for "no queue")
   int4* key4;      // [kRankSortMax] {queue, nsec, sec lo, sec hi}: one broadcast LDS.128 per compare
+  unsigned long long* ukey;  // [kRankSortMax] the same key packed into 64 bits when every key of the round fits
   int* perm;
   int32_t* r;
   float* gain;
@@ -70,6 +73,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
   {
     unsigned char* p = smem_raw;
     sm.key4 = reinterpret_cast<int4*>(p); p += 16 * kRankSortMax;
+    sm.ukey = reinterpret_cast<unsigned long long*>(p); p += 8 * kRankSortMax;
     sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Jp;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
     sm.klo = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
@@ -126,14 +130,26 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
         for (int x = tid; x < tot; x += nth) sm.table[x] = src[x];
       }
     }
+    bool fits = true;  // (queue, FirstStartTime) of every job packs into 64 bits, order preserved
     for (int i = tid; i < n; i += nth) {
       const int pr = a.priority[o + i];
       sm.prio[i] = pr;
       sm.kq[i] = (pr >= 0 && pr < Q) ? pr : Q;
       sm.khi[i] = a.first_sec[o + i];
       sm.klo[i] = a.first_nsec ? a.first_nsec[o + i] : 0;
-      if (n <= kRankSortMax)
+      if (n <= kRankSortMax) {
         sm.key4[i] = make_int4(sm.kq[i], sm.klo[i], (int)(uint32_t)(uint64_t)sm.khi[i], (int)(sm.khi[i] >> 32));
+        // 2 bits of queue | 32 bits of seconds | 30 bits of nanoseconds.  types.MaxTime (the
+        // never-started sentinel, far beyond 2^32 s) takes the seconds value 2^32-1, which no real
+        // time may use; anything else out of range sends the round to the general compare.
+        const long long sec = sm.khi[i];
+        const int ns = sm.klo[i];
+        const bool never = sec == kMaxTimeSec && ns == kMaxTimeNsec;
+        const bool real = sec >= 0 && sec < 0xFFFFFFFFll && ns >= 0 && ns < (1 << 30);
+        fits = fits && sm.kq[i] < 4 && (never || real);
+        const unsigned long long sf = never ? 0xFFFFFFFFull : (unsigned long long)sec;
+        sm.ukey[i] = ((unsigned long long)(unsigned)sm.kq[i] << 62) | (sf << 30) | (unsigned long long)(unsigned)ns;
+      }
       sm.mn[i] = a.min_proc[o + i];
       sm.mx[i] = a.max_proc[o + i];
       sm.r[i] = 0;
@@ -143,7 +159,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
       sm.misc[1] = 0;  // accepted in phase 3
       sm.misc[2] = 0;  // live jobs
     }
-    __syncthreads();
+    const bool packedKeys = __syncthreads_and(fits) != 0;
     auto S = [&](int i, int g) -> float {  // Info.Speedup[fmt.Sprint(g)], map miss => 0
       if (g < 0 || g >= W) return 0.0f;
       return tableInSmem ? sm.table[i * W + g] : a.speedup[(size_t)(o + i) * (size_t)W + (size_t)g];
@@ -163,7 +179,18 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
         if (klo[x] != klo[y]) return klo[x] < klo[y];
         return x < y;
       };
-      if (n <= kRankSortMax) {
+      if (n <= kRankSortMax && packedKeys) {
+        // rank sort on the 64-bit keys: rank(i) = #{j : u_j < u_i or (== and j < i)}
+        //                                        = #{j : u_j < u_i + [j < i]}   (u_i + 1 cannot overflow)
+        for (int i = tid; i < n; i += nth) {
+          const unsigned long long ui = sm.ukey[i];
+          int rank = 0;
+#pragma unroll 8
+          for (int j = 0; j < n; j++) rank += sm.ukey[j] < ui + (j < i ? 1ull : 0ull) ? 1 : 0;
+          sm.perm[rank] = i;
+        }
+        __syncthreads();
+      } else if (n <= kRankSortMax) {
         // rank sort on the packed records: rank(i) = #{j : key_j < key_i or (== and j < i)}
         for (int i = tid; i < n; i += nth) {
           const int4 ki = sm.key4[i];
@@ -326,7 +353,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
   }
 }
 
-size_t tir_fixed_smem(int Jp) { return (size_t)Jp * (8 + 4 * 10 + 2) + 16 * kRankSortMax + 8 * 4 + 4 * 8 + 32; }
+size_t tir_fixed_smem(int Jp) { return (size_t)Jp * (8 + 4 * 10 + 2) + 24 * kRankSortMax + 8 * 4 + 4 * 8 + 32; }
 
 }  // namespace
 
