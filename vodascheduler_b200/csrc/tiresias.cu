@@ -1,11 +1,13 @@
 // tiresias.cu — Tiresias (pkg/algorithm/tiresias.go:51-99) and ElasticTiresias
 // (pkg/algorithm/elastic_tiresias.go:37-159) for a batch of rounds (sm_100a).
 //
-// One CTA per round, per-job state in shared memory (and the round's speedup table too when it
-// fits).  Steps, with the reference lines they restate:
+// One CTA per round, per-job state in shared memory; the speedup table is read in place (a
+// round only looks up a few neighbouring entries per job).  Steps, with the reference lines they
+// restate:
 //   1. gain = S[min] / float32(min)                                   elastic_tiresias.go:58
 //   2. queues by Priority, each stable-sorted by FirstStartTime       :54-69  -> ONE block
-//      bitonic argsort on (queue, FirstStartTime, input index); jobs whose priority is outside
+//      argsort on (queue, FirstStartTime, input index) (rank sort on 64-bit packed keys for
+//      rounds up to 96 jobs whose times fit, bitonic otherwise); jobs whose priority is outside
 //      [0, Q) sort last and are not visited by phases 3-4
 //   3. give NumProc while it fits, queue by queue                     :75-85  -> warp skip-scan
 //   4. compaction of queues >= 1 to MinNumProc when pendings > threshold   :89-102
@@ -49,7 +51,6 @@ struct TirSmem {
   int* misc;       // [8]
   unsigned char* acc;
   unsigned char* live;
-  float* table;    // [n * W] when staged
 };
 
 struct Cand {
@@ -67,7 +68,7 @@ __device__ __forceinline__ bool better(const Cand& a, const Cand& b) {
   return a.stamp > b.stamp;
 }
 
-__global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp, int tableInSmem) {
+__global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   TirSmem sm;
   {
@@ -90,7 +91,6 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     sm.acc = p; p += (size_t)Jp;
     sm.live = p; p += (size_t)Jp;
     p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
-    sm.table = reinterpret_cast<float*>(p);
   }
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nth = blockDim.x;
@@ -108,28 +108,10 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
       continue;
     }
     __syncthreads();  // previous round's shared state is dead
-    // stage the speedup table (coalesced) and the per-job scalars
-    if (elastic && tableInSmem) {
-      const float* src = a.speedup + (size_t)o * (size_t)W;
-      const int tot = n * W;
-      if (((reinterpret_cast<uintptr_t>(src) & 7) == 0) && (tot & 1) == 0) {
-        // 8-byte loads, four in flight per thread: the staging loop is pure latency otherwise
-        const float2* s2 = reinterpret_cast<const float2*>(src);
-        float2* d2 = reinterpret_cast<float2*>(sm.table);
-        const int m = tot >> 1;
-        for (int x = tid; x < m; x += 4 * nth) {
-          float2 v[4];
-#pragma unroll
-          for (int u = 0; u < 4; u++)
-            if (x + u * nth < m) v[u] = s2[x + u * nth];
-#pragma unroll
-          for (int u = 0; u < 4; u++)
-            if (x + u * nth < m) d2[x + u * nth] = v[u];
-        }
-      } else {
-        for (int x = tid; x < tot; x += nth) sm.table[x] = src[x];
-      }
-    }
+    // per-job scalars.  The speedup table is NOT staged: a round looks up a handful of entries per
+    // job (S[min], S[min+1], S[n], S[n+1], then two per GPU handed out), neighbours in the row, so
+    // reading them in place touches one or two sectors per job where staging moved the whole
+    // 34-wide row through shared memory (measured 1.3x to 3x slower on 32..1024 jobs per round).
     bool fits = true;  // (queue, FirstStartTime) of every job packs into 64 bits, order preserved
     for (int i = tid; i < n; i += nth) {
       const int pr = a.priority[o + i];
@@ -162,7 +144,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp,
     const bool packedKeys = __syncthreads_and(fits) != 0;
     auto S = [&](int i, int g) -> float {  // Info.Speedup[fmt.Sprint(g)], map miss => 0
       if (g < 0 || g >= W) return 0.0f;
-      return tableInSmem ? sm.table[i * W + g] : a.speedup[(size_t)(o + i) * (size_t)W + (size_t)g];
+      return a.speedup[(size_t)(o + i) * (size_t)W + (size_t)g];
     };
     if (elastic)
       for (int i = tid; i < n; i += nth) sm.gain[i] = S(i, sm.mn[i]) / (float)sm.mn[i];  // :58
@@ -359,17 +341,13 @@ size_t tir_fixed_smem(int Jp) { return (size_t)Jp * (8 + 4 * 10 + 2) + 24 * kRan
 
 size_t tiresias_smem_bytes(const AllocArgs& a, bool* table_in_smem) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  size_t fixed = tir_fixed_smem(Jp);
-  size_t table = a.algo == VODA_ALGO_ELASTIC_TIRESIAS ? (size_t)a.max_jobs * (size_t)a.stride * 4 : 0;
-  bool in = table > 0 && fixed + table <= 200 * 1024;
-  if (table_in_smem) *table_in_smem = in;
-  return fixed + (in ? table : 0);
+  if (table_in_smem) *table_in_smem = false;  // the table is read in place
+  return tir_fixed_smem(Jp);
 }
 
 cudaError_t launch_tiresias(const AllocArgs& a, int sms, cudaStream_t stream) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  bool in = false;
-  const size_t smem = tiresias_smem_bytes(a, &in);
+  const size_t smem = tiresias_smem_bytes(a, nullptr);
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(tiresias_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -381,7 +359,7 @@ cudaError_t launch_tiresias(const AllocArgs& a, int sms, cudaStream_t stream) {
   if (perSm < 1) perSm = 1;
   int grid = sms * perSm;
   if (a.rounds < grid) grid = a.rounds;
-  tiresias_kernel<<<grid, threads, smem, stream>>>(a, Jp, in ? 1 : 0);
+  tiresias_kernel<<<grid, threads, smem, stream>>>(a, Jp);
   return cudaGetLastError();
 }
 
