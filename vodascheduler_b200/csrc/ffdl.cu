@@ -55,7 +55,10 @@ constexpr int kCells = 8;  // adjacent cells per thread: two float4 groups, a th
 // the speedup tables stop at 32), only every kCkpt-th row of P is stored, and the backtrack
 // recomputes the rows in between on the narrow band its walk can reach (kCkpt * kCkptGmax
 // cells at most).  That cuts the scratch traffic, the DP kernel's main memory cost, by kCkpt.
-constexpr int kCkpt = 4;
+#ifndef VODA_FFDL_CKPT
+#define VODA_FFDL_CKPT 4
+#endif
+constexpr int kCkpt = VODA_FFDL_CKPT;
 constexpr int kCkptGmax = 32;
 constexpr int kBand = kCkpt * kCkptGmax;  // cells per band row
 constexpr int kBandPad = kCkptGmax;       // -inf cells in front of a band row (columns below 0)
