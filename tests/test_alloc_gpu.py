@@ -130,6 +130,23 @@ def test_tiresias_times_outside_the_packed_key(ctx, oracle, algo):
     _same(ctx, oracle, b)
 
 
+@pytest.mark.parametrize("algo", ["FIFO", "ElasticFIFO", "FfDLOptimizer", "AFS-L"])
+def test_submit_times_outside_the_packed_key(ctx, oracle, algo):
+    """SubmitTime sorts run on 64-bit packed keys when the round's times lie in [0, 2^32) s and on
+    the general (seconds, nanoseconds, index) compare otherwise; both kinds of round, with ties."""
+    b = synth.jobs_batch(algo, rounds=64, jobs_per_round=50, total_gpu=70, ragged=True)
+    sec = b.submit_sec.copy()
+    ns = np.zeros(b.jobs, np.int32) if b.submit_nsec is None else b.submit_nsec.copy()
+    rnd = np.repeat(np.arange(b.rounds), np.diff(b.job_off))
+    j = np.arange(b.jobs)
+    sec[(rnd % 4 == 1) & (j % 6 == 0)] = -1_000_000              # before the epoch
+    sec[(rnd % 4 == 2) & (j % 5 == 0)] = (1 << 33) + 5           # beyond the 32-bit field
+    sec[(rnd % 4 == 3) & (j % 2 == 0)] = 1_790_000_123           # packable, heavy ties
+    ns[(rnd % 4 == 3)] = (j[(rnd % 4 == 3)] % 3) * 7
+    b.submit_sec, b.submit_nsec = sec, ns
+    _same(ctx, oracle, b)
+
+
 def test_esrjf_large_rounds(ctx, oracle):
     """The policy of BASELINE config 4 at 1024 jobs per round (bitonic sort + epoch fill)."""
     for algo in ("ElasticSRJF", "ElasticFIFO"):

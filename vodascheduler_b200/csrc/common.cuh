@@ -131,6 +131,43 @@ __device__ inline void block_ranksort_by(int* perm, int n, Less less) {
   __syncthreads();
 }
 
+// The same sort when every key of the round packs, order preserved, into ONE unsigned 64-bit
+// word: a bitonic network over (key, slot) pairs, slot = input index breaking ties (the result
+// of a stable sort by key).  A compare-exchange is two LDS.64, two LDS.32, one 64-bit compare and
+// the conditional stores, against a dozen dependent shared loads in the indirect argsort; each
+// thread takes whole pairs, so no thread idles on the "upper" element.  The caller fills
+// key[0..P) (slots >= n: all ones, which sorts them last in slot order) before the call; perm is
+// written here.  All threads of the CTA must call it.
+__device__ inline void block_sort_kv(unsigned long long* key, int* perm, int P) {
+  for (int i = threadIdx.x; i < P; i += blockDim.x) perm[i] = i;
+  __syncthreads();
+  for (int k = 2; k <= P; k <<= 1) {
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < (P >> 1); t += blockDim.x) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // the pair's lower slot (bit j clear)
+        const int ixj = i | j;
+        const unsigned long long ka = key[i], kb = key[ixj];
+        const int pa = perm[i], pb = perm[ixj];
+        const bool up = (i & k) == 0;
+        const bool a_after_b = kb < ka || (kb == ka && pb < pa);
+        if (a_after_b == up) {
+          key[i] = kb;
+          key[ixj] = ka;
+          perm[i] = pb;
+          perm[ixj] = pa;
+        }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// (seconds, nanoseconds) -> one word, when it fits: seconds in [0, 2^32), nanoseconds in [0, 2^30).
+__device__ __forceinline__ bool pack_time_key(long long sec, int nsec, unsigned long long* out) {
+  *out = ((unsigned long long)sec << 30) | (unsigned long long)(unsigned)nsec;
+  return sec >= 0 && sec < (1ll << 32) && nsec >= 0 && nsec < (1 << 30);
+}
+
 __device__ inline void block_argsort(const int64_t* hi, const int32_t* lo, int* perm, int n, int P) {
   block_argsort_by(perm, P, [=](int a, int b) { return key_less(hi, lo, n, a, b); });
 }

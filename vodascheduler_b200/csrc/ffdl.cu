@@ -433,13 +433,29 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
       continue;
     }
     __syncthreads();  // the previous round's shared state is dead
-    // 1. stable sort by SubmitTime
-    for (int i = tid; i < n; i += kThreads) {
-      sm.khi[i] = a.submit_sec ? a.submit_sec[o + i] : 0;
-      sm.klo[i] = a.submit_nsec ? a.submit_nsec[o + i] : 0;
+    // 1. stable sort by SubmitTime: on 64-bit packed keys when every time of the round fits
+    //    (seconds in [0, 2^32)), by the general argsort otherwise
+    {
+      const int P = next_pow2(n);
+      unsigned long long* ukey = reinterpret_cast<unsigned long long*>(sm.khi);
+      bool fits = true;
+      for (int i = tid; i < P; i += kThreads) {
+        unsigned long long u = ~0ull;
+        if (i < n)
+          fits = pack_time_key(a.submit_sec ? a.submit_sec[o + i] : 0, a.submit_nsec ? a.submit_nsec[o + i] : 0, &u) && fits;
+        ukey[i] = u;
+      }
+      if (__syncthreads_and(fits)) {
+        block_sort_kv(ukey, sm.perm, P);
+      } else {
+        for (int i = tid; i < n; i += kThreads) {
+          sm.khi[i] = a.submit_sec ? a.submit_sec[o + i] : 0;
+          sm.klo[i] = a.submit_nsec ? a.submit_nsec[o + i] : 0;
+        }
+        __syncthreads();
+        block_argsort(sm.khi, sm.klo, sm.perm, n, P);
+      }
     }
-    __syncthreads();
-    block_argsort(sm.khi, sm.klo, sm.perm, n, next_pow2(n));
     // 2. trim, 3-4. DP rows
     const int J = min(n, K);
     const int KT = (K + kCells - 1) / kCells;

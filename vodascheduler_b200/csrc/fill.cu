@@ -70,18 +70,34 @@ __global__ void __launch_bounds__(kThreads) fill_kernel(AllocArgs a, int Jp) {
       if (tid == 0) a.out_status[r] = VODA_ST_BOUND;
       continue;
     }
-    // 1. keys + stable sort
-    for (int i = tid; i < n; i += kThreads) {
-      if (byRemaining) {
-        sm.khi[i] = f32_order_key(a.remaining_sec[o + i]);
-        sm.klo[i] = 0;
+    // 1. keys + stable sort.  The float32 remaining time always packs into a 64-bit key, a
+    //    SubmitTime does when it lies in [0, 2^32) s (else the round takes the general argsort).
+    const int P = next_pow2(n > 0 ? n : 1);
+    unsigned long long* ukey = reinterpret_cast<unsigned long long*>(sm.khi);
+    bool fits = true;
+    for (int i = tid; i < P; i += kThreads) {
+      if (i >= n) {
+        ukey[i] = ~0ull;
+      } else if (byRemaining) {
+        ukey[i] = (unsigned long long)(f32_order_key(a.remaining_sec[o + i]) + (1ll << 31));
       } else {
+        const long long sec = a.submit_sec[o + i];
+        const int ns = a.submit_nsec ? a.submit_nsec[o + i] : 0;
+        unsigned long long u;
+        fits = pack_time_key(sec, ns, &u) && fits;
+        ukey[i] = u;
+      }
+    }
+    if (__syncthreads_and(fits)) {
+      block_sort_kv(ukey, sm.perm, P);
+    } else {  // (only SubmitTime keys get here)
+      for (int i = tid; i < n; i += kThreads) {
         sm.khi[i] = a.submit_sec[o + i];
         sm.klo[i] = a.submit_nsec ? a.submit_nsec[o + i] : 0;
       }
+      __syncthreads();
+      block_argsort(sm.khi, sm.klo, sm.perm, n, P);
     }
-    __syncthreads();
-    block_argsort(sm.khi, sm.klo, sm.perm, n, next_pow2(n > 0 ? n : 1));
     for (int i = tid; i < n; i += kThreads) {
       const int j = o + sm.perm[i];
       sm.mn[i] = a.min_proc[j];
