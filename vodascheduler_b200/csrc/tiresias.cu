@@ -39,7 +39,7 @@ struct TirSmem {
   int32_t* klo;
   int32_t* kq;     // queue index (Q for "no queue")
   int4* key4;      // [kRankSortMax] {queue, nsec, sec lo, sec hi}: one broadcast LDS.128 per compare
-  unsigned long long* ukey;  // [kRankSortMax] the same key packed into 64 bits when every key of the round fits
+  unsigned long long* ukey;  // [Jp] the same key packed into 64 bits when every key of the round fits
   int* perm;
   int32_t* r;
   float* gain;
@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
   {
     unsigned char* p = smem_raw;
     sm.key4 = reinterpret_cast<int4*>(p); p += 16 * kRankSortMax;
-    sm.ukey = reinterpret_cast<unsigned long long*>(p); p += 8 * kRankSortMax;
+    sm.ukey = reinterpret_cast<unsigned long long*>(p); p += 8 * (size_t)Jp;
     sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Jp;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
     sm.klo = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
@@ -119,8 +119,9 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
       sm.kq[i] = (pr >= 0 && pr < Q) ? pr : Q;
       sm.khi[i] = a.first_sec[o + i];
       sm.klo[i] = a.first_nsec ? a.first_nsec[o + i] : 0;
-      if (n <= kRankSortMax) {
+      if (n <= kRankSortMax)
         sm.key4[i] = make_int4(sm.kq[i], sm.klo[i], (int)(uint32_t)(uint64_t)sm.khi[i], (int)(sm.khi[i] >> 32));
+      {
         // 2 bits of queue | 32 bits of seconds | 30 bits of nanoseconds.  types.MaxTime (the
         // never-started sentinel, far beyond 2^32 s) takes the seconds value 2^32-1, which no real
         // time may use; anything else out of range sends the round to the general compare.
@@ -172,6 +173,12 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
           sm.perm[rank] = i;
         }
         __syncthreads();
+      } else if (packedKeys) {
+        // larger rounds: bitonic network over (64-bit key, slot) pairs
+        const int P = next_pow2(n > 0 ? n : 1);
+        for (int i = n + tid; i < P; i += nth) sm.ukey[i] = ~0ull;
+        __syncthreads();
+        block_sort_kv(sm.ukey, sm.perm, P);
       } else if (n <= kRankSortMax) {
         // rank sort on the packed records: rank(i) = #{j : key_j < key_i or (== and j < i)}
         for (int i = tid; i < n; i += nth) {
@@ -335,7 +342,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
   }
 }
 
-size_t tir_fixed_smem(int Jp) { return (size_t)Jp * (8 + 4 * 10 + 2) + 24 * kRankSortMax + 8 * 4 + 4 * 8 + 32; }
+size_t tir_fixed_smem(int Jp) { return (size_t)Jp * (8 + 8 + 4 * 10 + 2) + 16 * kRankSortMax + 8 * 4 + 4 * 8 + 32; }
 
 }  // namespace
 
