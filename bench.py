@@ -41,8 +41,10 @@ WORKLOADS = {
     "ffdl_c2": dict(kind="alloc", algo="FfDLOptimizer", rounds=10000, jobs=256, total=1024,
                     desc="FfDL Optimizer DP allocation, 10k batched rounds of 256 jobs x 1024 GPUs (BASELINE configs[1])"),
     # configs[2]
-    "afsl_c3": dict(kind="alloc", algo="AFS-L", rounds=2000, jobs=1024, total=4096,
-                    desc="AFS-L greedy allocation, batched rounds of 1024 jobs x 4096 GPUs (BASELINE configs[2], 2k-round batch)"),
+    # 2368 rounds = 4 full waves of the kernel's 592 resident CTAs on a B200 (a round is one long
+    # dependent chain, so a partial last wave costs a whole wave: 2000 rounds measure 13 % lower)
+    "afsl_c3": dict(kind="alloc", algo="AFS-L", rounds=2368, jobs=1024, total=4096,
+                    desc="AFS-L greedy allocation, batched rounds of 1024 jobs x 4096 GPUs (BASELINE configs[2], 2368-round batch)"),
     # configs[0] batched
     "tiresias_c1": dict(kind="alloc", algo="ElasticTiresias", rounds=200000, jobs=64, total=16,
                         desc="Elastic-Tiresias, batched rounds of 64 jobs on 16 GPUs (BASELINE configs[0], 200k-round batch)"),
