@@ -473,18 +473,15 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
 }
 
 // Kernel B: backtrack (:116-125) + deferred validateResult (:42).
-// The walk is a chain of J dependent steps (row j-1 is read at k - g_j): it is all latency, and
-// its length per step is what the kernel's time is made of (measured: the same 0.4 ms for 2.5k,
-// 5k or 10k rounds).  ONE WARP walks one round, every round of the batch in flight at once.  At
-// row j the warp re-evaluates the reference's inner loop (:93-103) for the single cell (j, k),
+// The walk is a chain of J dependent steps (row j-1 is read at k - g_j).  ONE WARP walks one
+// round.  At row j it re-evaluates the reference's inner loop (:93-103) for the single cell (j, k),
 //   best = -10000, sol = 0;  for g = 1 .. min(max_j, K, k):  p = S_j[g] + P[j-1][k-g];
 //   if p > best { best = p; sol = g }
-// 32 candidates at a time, one per lane: the P values are adjacent floats of the stored row (one
-// coalesced load), and the strict-'>' scan in increasing g is "the first lane that holds the
-// maximum": an order-preserving integer key, one REDUX.MAX and one ballot.  P[j-1][x] comes
-// from the stored row, its saturated constant, or row 0 = 0.  Only that load depends on the
-// position: the row record and the S values of the next row are fetched one row ahead, and the
-// stretch of P the walk can reach a few rows from now is prefetched into L2.  Then the warp
+// 32 candidates at a time, one per lane: the P values are adjacent floats of row j-1, and the
+// strict-'>' scan in increasing g is "the first lane that holds the maximum": an order-preserving
+// integer key, one REDUX.MAX and one ballot.  P[j-1][x] comes from the stored row, its saturated
+// constant, or row 0 = 0; in a checkpointed round from the band recomputed in shared memory
+// (ffdl_walk_sparse), otherwise straight from the slab (ffdl_walk_dense).  Then the warp
 // validates its round with coalesced reads.
 constexpr int kBtThreads = 128;
 constexpr int kBtAhead = 3;  // rows of lookahead for the L2 prefetch of P
@@ -615,83 +612,83 @@ __device__ __forceinline__ void ffdl_walk_sparse(const AllocArgs& a, const FfdlS
   }
 }
 
-#ifndef VODA_BT_MINBLOCKS
-#define VODA_BT_MINBLOCKS 8
-#endif
-__global__ void __launch_bounds__(kBtThreads, VODA_BT_MINBLOCKS)
+// The walk of a round that stored every row of P (some job can take more than kCkptGmax GPUs):
+// row by row, 32 candidates at a time; the row record and the S values of the next row are
+// fetched one row ahead and the stretch of P reachable a few rows from now is prefetched into L2.
+__device__ __forceinline__ void ffdl_walk_dense(const AllocArgs& a, const FfdlScratch& sc, int rr, int o, int J, int K,
+                                                int lane) {
+  const unsigned full = 0xffffffffu;
+  const float* slab = sc.P + (size_t)rr * sc.slabFloats;
+  const float* gsrows = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)sc.SW;
+  const int4* grows = reinterpret_cast<const int4*>(sc.rows + (size_t)rr * (size_t)sc.Jcap);  // job, gmax, klim, c
+  int32_t* out = a.out_gpus + o;
+  const int SW = sc.SW;
+  const int W = a.stride;
+  const int rowFloats = (int)sc.rowFloats;
+  const int slane = min(lane, SW - 1);
+  const int4 none = make_int4(0, 0, 0, 0);
+  const unsigned keyFloor = f32_key(-10000.0f);
+  int k = K;
+  int4 rc = grows[J - 1];                  // row j
+  int4 rp = J >= 2 ? grows[J - 2] : none;  // row j-1: its klim and c describe the row that is read
+  float s1 = gsrows[(J - 1) * SW + slane];  // S_j[1 + lane]
+  for (int j = J; j >= 1; j--) {
+    // one row ahead (none of this depends on the position)
+    const int4 rpp = j >= 3 ? grows[j - 3] : none;
+    const float s1next = j >= 2 ? gsrows[(j - 2) * SW + slane] : 0.0f;
+    // the position can only drift down, by the g's chosen on the way
+    if (lane < 4 && j - 2 - kBtAhead >= 0) prefetch_l2(slab + (j - 2 - kBtAhead) * rowFloats + max(k - 1 - 32 * lane, 0));
+    const int gm = min(rc.y, k);                           // candidates g = 1 .. gm (k-g >= 0)
+    const float* prow = slab + max(j - 2, 0) * rowFloats;  // P[j-1][x] at prow[x-1] (j >= 2)
+    const int klp = rp.z;
+    const float cp = __int_as_float(rp.w);
+    unsigned bestKey = keyFloor;  // best = -10000
+    int sol = 0;
+    for (int g0 = 1; g0 <= gm; g0 += 32) {
+      const int g = g0 + lane;
+      const int x = k - g;
+      // unconditional loads on clamped, always-valid addresses; the cases are sorted out below
+      const float pv = prow[max(x, 1) - 1];
+      const float sv = g0 == 1 ? s1 : gsrows[(j - 1) * SW + min(g, SW) - 1];
+      const float sg = g <= W - 1 ? sv : 0.0f;  // a g the table does not hold: Go map miss
+      float pg = x <= 0 ? -10000.0f : (x >= klp ? cp : pv);
+      if (j == 1) pg = 0.0f;  // row 0
+      const float p = sg + pg;
+      // strict '>' in increasing g == the first lane holding the maximum; a NaN never wins
+      const unsigned key = (g <= gm && p == p) ? f32_key(p) : 0u;
+      const unsigned top = __reduce_max_sync(full, key);
+      if (top > bestKey) {
+        bestKey = top;
+        sol = g0 + __ffs((int)__ballot_sync(full, key == top)) - 1;
+      }
+    }
+    if (lane == 0) out[rc.x] = sol;
+    k -= sol;
+    rc = rp;
+    rp = rpp;
+    s1 = s1next;
+  }
+}
+
+__global__ void __launch_bounds__(kBtThreads, 8)
     ffdl_backtrack_kernel(AllocArgs a, int r0, int count, FfdlScratch sc) {
   __shared__ float band[kBtThreads / 32][kCkpt][kBandRow];
   __shared__ float ssm[kBtThreads / 32][kCkpt][32];
   for (int i = threadIdx.x; i < (kBtThreads / 32) * kCkpt * kBandPad; i += kBtThreads)  // the pads, written once
     band[i / (kCkpt * kBandPad)][(i / kBandPad) % kCkpt][i % kBandPad] = VODA_NEG_INF;
   __syncthreads();
-  constexpr int LANES = 32;
-  const int wlane = threadIdx.x & 31;
-  const int lane = wlane;
-  const int shift = 0;
   const unsigned full = 0xffffffffu;
-  const int rr = blockIdx.x * (kBtThreads / 32) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int rr = blockIdx.x * (kBtThreads / 32) + warp;  // a warp per round
   if (rr >= count) return;
   const int r = r0 + rr;
   const int o = a.job_off[r] - a.job_base;
   const int n = a.job_off[r + 1] - a.job_off[r];
   const FfdlMeta meta = sc.meta[rr];
   // ---- phase 1: the walk
-  if (meta.st == VODA_ST_OK && meta.J > 0 && meta.sparse) {
-    ffdl_walk_sparse(a, sc, rr, o, meta.J, meta.K, lane, band[threadIdx.x >> 5], ssm[threadIdx.x >> 5]);
-  } else if (meta.st == VODA_ST_OK && meta.J > 0) {
-    const float* slab = sc.P + (size_t)rr * sc.slabFloats;
-    const float* gsrows = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)sc.SW;
-    const int4* grows = reinterpret_cast<const int4*>(sc.rows + (size_t)rr * (size_t)sc.Jcap);  // job, gmax, klim, c
-    int32_t* out = a.out_gpus + o;
-    const int SW = sc.SW;
-    const int W = a.stride;
-    const int rowFloats = (int)sc.rowFloats;
-    const int slane = min(lane, SW - 1);
-    const int4 none = make_int4(0, 0, 0, 0);
-    const unsigned keyFloor = f32_key(-10000.0f);
-    const int J = meta.J;
-    int k = meta.K;
-    int4 rc = grows[J - 1];                  // row j
-    int4 rp = J >= 2 ? grows[J - 2] : none;  // row j-1: its klim and c describe the row that is read
-    float s1 = gsrows[(J - 1) * SW + slane];  // S_j[1 + lane]
-    for (int j = J; j >= 1; j--) {
-      // one row ahead (none of this depends on the position)
-      const int4 rpp = j >= 3 ? grows[j - 3] : none;
-      const float s1next = j >= 2 ? gsrows[(j - 2) * SW + slane] : 0.0f;
-      // the stretch of P the walk will read kBtAhead rows from now: the position can only drift
-      // down, by the g's chosen on the way (four lines cover 128 cells)
-      if (lane < 4 && j - 2 - kBtAhead >= 0) prefetch_l2(slab + (j - 2 - kBtAhead) * rowFloats + max(k - 1 - 32 * lane, 0));
-      const int gm = min(rc.y, k);                           // candidates g = 1 .. gm (k-g >= 0)
-      const float* prow = slab + max(j - 2, 0) * rowFloats;  // P[j-1][x] at prow[x-1] (j >= 2)
-      const int klp = rp.z;
-      const float cp = __int_as_float(rp.w);
-      unsigned bestKey = keyFloor;  // best = -10000
-      int sol = 0;
-      for (int g0 = 1; g0 <= gm; g0 += LANES) {
-        const int g = g0 + lane;
-        const int x = k - g;
-        // unconditional loads on clamped, always-valid addresses; the cases are sorted out below
-        const float pv = prow[max(x, 1) - 1];
-        const float sv = g0 == 1 ? s1 : gsrows[(j - 1) * SW + min(g, SW) - 1];
-        const float sg = g <= W - 1 ? sv : 0.0f;  // a g the table does not hold: Go map miss
-        float pg = x <= 0 ? -10000.0f : (x >= klp ? cp : pv);
-        if (j == 1) pg = 0.0f;  // row 0
-        const float p = sg + pg;
-        // strict '>' in increasing g == the first lane holding the maximum; a NaN never wins
-        const unsigned key = (g <= gm && p == p) ? f32_key(p) : 0u;
-        const unsigned top = __reduce_max_sync(full, key);
-        if (top > bestKey) {
-          bestKey = top;
-          sol = g0 + __ffs((int)(__ballot_sync(full, key == top) >> shift)) - 1;
-        }
-      }
-      if (lane == 0) out[rc.x] = sol;
-      k -= sol;
-      rc = rp;
-      rp = rpp;
-      s1 = s1next;
-    }
+  if (meta.st == VODA_ST_OK && meta.J > 0) {
+    if (meta.sparse) ffdl_walk_sparse(a, sc, rr, o, meta.J, meta.K, lane, band[warp], ssm[warp]);
+    else ffdl_walk_dense(a, sc, rr, o, meta.J, meta.K, lane);
   }
   __syncwarp(full);
   // ---- phase 2: validateResult (utils.go:18-42); a panic it raises replaces the one in flight
@@ -701,11 +698,11 @@ __global__ void __launch_bounds__(kBtThreads, VODA_BT_MINBLOCKS)
   }
   int worst = 99;
   long long sum = 0;
-  for (int base = 0; base < n; base += LANES * 8) {  // 24 loads in flight per lane, then the checks
+  for (int base = 0; base < n; base += 32 * 8) {  // 24 loads in flight per lane, then the checks
     int v[8], mn[8], mx[8];
 #pragma unroll
     for (int u = 0; u < 8; u++) {
-      const int i = base + LANES * u + lane;
+      const int i = base + 32 * u + lane;
       const bool ok = i < n;
       v[u] = ok ? a.out_gpus[o + i] : 0;
       mn[u] = ok ? a.min_proc[o + i] : 0;
@@ -721,7 +718,7 @@ __global__ void __launch_bounds__(kBtThreads, VODA_BT_MINBLOCKS)
       sum += v[u];
     }
   }
-  for (int d = LANES / 2; d > 0; d >>= 1) {
+  for (int d = 16; d > 0; d >>= 1) {
     worst = min(worst, __shfl_xor_sync(full, worst, d));
     sum += __shfl_xor_sync(full, sum, d);
   }
