@@ -238,6 +238,35 @@ typedef struct {
 int voda_place(voda_ctx* ctx, const voda_place_batch* host_batch, const voda_place_out* host_out);
 int voda_place_dev(voda_ctx* ctx, const voda_place_batch* dev_batch, const voda_place_out* dev_out);
 
+/* ---- speedup-curve builder ---------------------------------------------------------------
+ * Replaces the arithmetic of python/metrics_collector/metrics_collector.py:131-167
+ * (_update_time_metric, _update_speedup, _update_efficiency) for a batch of jobs: the curves
+ * the allocation policies read as Info.Speedup.  Job j owns the records
+ * [rec_off[j], rec_off[j+1]) of its metrics CSV, in file order: workers[i] = the `workers`
+ * column, epoch_time_sec[i] = the `epoch_time_sec` column.  Outputs, float64, dense over the
+ * worker count k = 0 .. width-1 (the dictionaries' keys "0" .. str(width-1)), starting from
+ * CreateBaseJobInfo's linear defaults (pkg/common/mongo/mongo.go:76-100):
+ *   out_epoch_time[j*width + k]   mean epoch time with k workers (pandas: pairwise sum / count),
+ *                                 1.0 where the job has no record with k workers, 0 at k = 0
+ *   out_speedup[j*width + k]      epoch_time[1] / epoch_time[k], 0 at k = 0
+ *   out_efficiency[j*width + k]   speedup[k] / k, 0 at k = 0
+ *   out_status[j]                 VODA_ST_OK, or VODA_ST_BOUND when a record's worker count is
+ *                                 outside [0, width) (the outputs of that job ignore such records)
+ * Bit-identical to the reference run through pandas / numpy (tests/golden/curve_kats.json).
+ */
+typedef struct {
+  int32_t jobs;
+  int32_t width;                 /* 34 = keys "0" .. "33" of CreateBaseJobInfo */
+  const int32_t* rec_off;        /* [jobs + 1] */
+  const int32_t* workers;        /* [records] */
+  const double* epoch_time_sec;  /* [records] */
+} voda_curve_batch;
+
+int voda_build_curves(voda_ctx* ctx, const voda_curve_batch* host_batch, double* out_epoch_time,
+                      double* out_speedup, double* out_efficiency, int32_t* out_status);
+int voda_build_curves_dev(voda_ctx* ctx, const voda_curve_batch* dev_batch, double* d_out_epoch_time,
+                          double* d_out_speedup, double* d_out_efficiency, int32_t* d_out_status);
+
 #ifdef __cplusplus
 }
 #endif

@@ -55,6 +55,11 @@ class PlaceOutStruct(C.Structure):
 
 
 # every symbol include/voda_accel.h declares: name -> (restype, argtypes)
+class CurveBatchStruct(C.Structure):  # voda_curve_batch
+    _fields_ = [("jobs", C.c_int32), ("width", C.c_int32), ("rec_off", C.c_void_p), ("workers", C.c_void_p),
+                ("epoch_time_sec", C.c_void_p)]
+
+
 PROTOTYPES = {
     "voda_ctx_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "voda_ctx_destroy": (None, [C.c_void_p]),
@@ -77,6 +82,10 @@ PROTOTYPES = {
     "voda_munkres_max_dev": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "voda_place": (C.c_int, [C.c_void_p, C.POINTER(PlaceBatchStruct), C.POINTER(PlaceOutStruct)]),
     "voda_place_dev": (C.c_int, [C.c_void_p, C.POINTER(PlaceBatchStruct), C.POINTER(PlaceOutStruct)]),
+    "voda_build_curves": (C.c_int, [C.c_void_p, C.POINTER(CurveBatchStruct), C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
+    "voda_build_curves_dev": (C.c_int, [C.c_void_p, C.POINTER(CurveBatchStruct), C.c_void_p, C.c_void_p, C.c_void_p,
+                                        C.c_void_p]),
 }
 
 

@@ -135,6 +135,22 @@ class Context:
         s = dev_batch.struct()
         self._check(self._lib.voda_place_dev(self._h, C.byref(s), C.byref(dev_out_struct)), "voda_place_dev")
 
+    # -- speedup curves ----------------------------------------------------------------
+    def build_curves(self, rec_off, workers, epoch_time_sec, width=34):
+        """metrics_collector.py:131-167 for a batch of jobs (host arrays in, host arrays out):
+        returns (epoch_time, speedup, efficiency) as [jobs, width] float64 and status [jobs]."""
+        rec_off = np.ascontiguousarray(rec_off, np.int32)
+        workers = np.ascontiguousarray(workers, np.int32)
+        t = np.ascontiguousarray(epoch_time_sec, np.float64)
+        jobs = max(0, rec_off.size - 1)
+        et, sp, ef = (np.zeros((max(1, jobs), width), np.float64) for _ in range(3))
+        st = np.full(max(1, jobs), -1, np.int32)
+        s = _abi.CurveBatchStruct(jobs, width, rec_off.ctypes.data, workers.ctypes.data if workers.size else None,
+                                  t.ctypes.data if t.size else None)
+        self._check(self._lib.voda_build_curves(self._h, C.byref(s), et.ctypes.data, sp.ctypes.data, ef.ctypes.data,
+                                                st.ctypes.data), "voda_build_curves")
+        return et[:jobs], sp[:jobs], ef[:jobs], st[:jobs]
+
     # -- pinned host memory ------------------------------------------------------------
     def pinned(self, shape, dtype):
         """numpy array backed by voda_host_alloc (page-locked) memory."""

@@ -632,4 +632,57 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   return VODA_OK;
 }
 
+static int check_curves(voda_ctx* ctx, const voda_curve_batch* b, const void* o1, const void* o2, const void* o3,
+                        const void* st) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  if (!b) return fail(ctx, VODA_E_INVALID, "null batch");
+  if (b->jobs < 0 || b->width < 2) return fail(ctx, VODA_E_INVALID, "curves: jobs >= 0 and width >= 2 required");
+  if (b->jobs > 0 && (!b->rec_off || !o1 || !o2 || !o3 || !st)) return fail(ctx, VODA_E_INVALID, "null buffer");
+  return VODA_OK;
+}
+
+int voda_build_curves_dev(voda_ctx* ctx, const voda_curve_batch* b, double* d_time, double* d_speedup,
+                          double* d_eff, int32_t* d_status) {
+  int rc = check_curves(ctx, b, d_time, d_speedup, d_eff, d_status);
+  if (rc || b->jobs == 0) return rc;
+  CU(cudaSetDevice(ctx->device));
+  CU(launch_curves(b->jobs, b->rec_off, b->workers, b->epoch_time_sec, b->width, d_time, d_speedup, d_eff, d_status,
+                   ctx->stream));
+  ctx->launches += 1;
+  return VODA_OK;
+}
+
+int voda_build_curves(voda_ctx* ctx, const voda_curve_batch* b, double* out_time, double* out_speedup,
+                      double* out_eff, int32_t* out_status) {
+  int rc = check_curves(ctx, b, out_time, out_speedup, out_eff, out_status);
+  if (rc || b->jobs == 0) return rc;
+  if (b->rec_off[0] != 0) return fail(ctx, VODA_E_INVALID, "rec_off[0] must be 0");
+  const size_t J = (size_t)b->jobs, W = (size_t)b->width;
+  const size_t recs = (size_t)b->rec_off[J];
+  if (recs > 0 && (!b->workers || !b->epoch_time_sec)) return fail(ctx, VODA_E_INVALID, "null record arrays");
+  CU(cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->pipe[0];
+  const size_t o_off = 0, o_w = align256(4 * (J + 1)), o_t = o_w + align256(4 * recs), o_et = o_t + align256(8 * recs),
+               o_sp = o_et + align256(8 * J * W), o_ef = o_sp + align256(8 * J * W), o_st = o_ef + align256(8 * J * W),
+               total = o_st + align256(4 * J);
+  rc = ensure(ctx, ctx->stage[0], total, s);
+  if (rc) return rc;
+  char* base = (char*)ctx->stage[0].p;
+  CU(cudaMemcpyAsync(base + o_off, b->rec_off, 4 * (J + 1), cudaMemcpyHostToDevice, s));
+  if (recs) {
+    CU(cudaMemcpyAsync(base + o_w, b->workers, 4 * recs, cudaMemcpyHostToDevice, s));
+    CU(cudaMemcpyAsync(base + o_t, b->epoch_time_sec, 8 * recs, cudaMemcpyHostToDevice, s));
+  }
+  CU(launch_curves(b->jobs, (const int32_t*)(base + o_off), (const int32_t*)(base + o_w), (const double*)(base + o_t),
+                   b->width, (double*)(base + o_et), (double*)(base + o_sp), (double*)(base + o_ef),
+                   (int32_t*)(base + o_st), s));
+  ctx->launches += 1;
+  CU(cudaMemcpyAsync(out_time, base + o_et, 8 * J * W, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(out_speedup, base + o_sp, 8 * J * W, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(out_eff, base + o_ef, 8 * J * W, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(out_status, base + o_st, 4 * J, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  return VODA_OK;
+}
+
 }  // extern "C"

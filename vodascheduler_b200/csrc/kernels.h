@@ -35,4 +35,9 @@ size_t place_smem_bytes(const PlaceArgs& a);
 size_t place_scratch_bytes(const PlaceArgs& a, int sms);
 cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream);
 
+// speedup-curve builder (curves.cu)
+cudaError_t launch_curves(int jobs, const int32_t* rec_off, const int32_t* workers, const double* t, int W,
+                          double* out_time, double* out_speedup, double* out_eff, int32_t* out_status,
+                          cudaStream_t stream);
+
 }  // namespace voda
