@@ -9,18 +9,25 @@
 // of that worker count in record order (blocks of up to 128 elements with eight running
 // accumulators, halves rounded down to a multiple of eight above that), restated here as a
 // recursion over a cursor that walks the job's records once, left to right.
-// One warp per job, one lane per worker count (counts beyond 31 in further passes).
+// One warp per job: a coalesced pass counts the records of every worker count, then one lane per
+// worker count that occurs walks the records and sums its own.
 #include "common.cuh"
 #include "kernels.h"
 
 namespace voda {
 namespace {
 
+constexpr int kCntCap = 64;  // worker counts with a shared-memory counter per warp
+
+constexpr int kStageCap = 256;  // records per job that fit the warp's staging buffer
+
 struct Cursor {  // the records of one job with workers == w, in record order
+  const double* run;  // non-null: the values already gathered into one contiguous run
   const int32_t* workers;
   const double* t;
   int pos, end, w;
   __device__ double next() {
+    if (run) return run[pos++];
     while (pos < end && workers[pos] != w) pos++;
     return pos < end ? t[pos++] : 0.0;
   }
@@ -67,12 +74,60 @@ __global__ void __launch_bounds__(128) curves_kernel(int jobs, const int32_t* __
   double* et = out_time + (size_t)job * W;
   double* sp = out_speedup + (size_t)job * W;
   double* ef = out_eff + (size_t)job * W;
+  // how many records each worker count has: one coalesced pass with shared-memory counters
+  // when the table is small enough for them (kCntCap slots per warp), a scan per lane otherwise
+  __shared__ int cntS[4][kCntCap];
+  int* cnts = cntS[threadIdx.x >> 5];
+  const bool counted = W <= kCntCap;
+  if (counted) {
+    for (int w = lane; w < W; w += 32) cnts[w] = 0;
+    __syncwarp();
+    for (int i = r0 + lane; i < r1; i += 32) {
+      const int w = workers[i];
+      if (w >= 0 && w < W) atomicAdd(&cnts[w], 1);
+    }
+    __syncwarp();
+  }
+  // small jobs: a second coalesced pass gathers the epoch times of every worker count into its
+  // own contiguous run of the staging buffer, in record order (stable: a record's slot is its
+  // count's base + the number of earlier records with the same count)
+  __shared__ double stageS[4][kStageCap];
+  __shared__ int baseS[4][kCntCap];
+  double* stage = stageS[threadIdx.x >> 5];
+  int* base = baseS[threadIdx.x >> 5];
+  const bool staged = counted && (r1 - r0) <= kStageCap;
+  if (staged) {
+    if (lane == 0) {
+      int acc = 0;
+      for (int w = 0; w < W; w++) {
+        base[w] = acc;
+        acc += cnts[w];
+      }
+    }
+    __syncwarp();
+    for (int i0 = r0; i0 < r1; i0 += 32) {
+      const int i = i0 + lane;
+      const int w = i < r1 ? workers[i] : -1;
+      const bool ok = w >= 0 && w < W;
+      const unsigned same = __match_any_sync(0xffffffffu, ok ? w : -1 - lane);
+      if (ok) {
+        const int rank = __popc(same & ((1u << lane) - 1u));
+        stage[base[w] + rank] = t[i];
+      }
+      __syncwarp();
+      if (ok && (same & ((1u << lane) - 1u)) == 0) base[w] += __popc(same);  // the run's first lane
+      __syncwarp();
+    }
+    // base[w] now points one past the run of w
+  }
   for (int w = lane; w < W; w += 32) {
     double v = w == 0 ? 0.0 : 1.0;  // CreateBaseJobInfo
     int cnt = 0;
-    for (int i = r0; i < r1; i++) cnt += workers[i] == w;
+    if (counted) cnt = cnts[w];
+    else
+      for (int i = r0; i < r1; i++) cnt += workers[i] == w;
     if (cnt > 0) {
-      Cursor c{workers, t, r0, r1, w};
+      Cursor c{staged ? stage + (base[w] - cnt) : nullptr, workers, t, staged ? 0 : r0, r1, w};
       v = pairwise_sum(c, cnt) / (double)cnt;
     }
     et[w] = v;
