@@ -267,6 +267,60 @@ int voda_build_curves(voda_ctx* ctx, const voda_curve_batch* host_batch, double*
 int voda_build_curves_dev(voda_ctx* ctx, const voda_curve_batch* dev_batch, double* d_out_epoch_time,
                           double* d_out_speedup, double* d_out_efficiency, int32_t* d_out_status);
 
+/* ---- scheduler bookkeeping between rounds ---------------------------------------------------
+ * voda_tick replaces the loop body of Scheduler.updateTimeMetrics
+ * (pkg/scheduler/scheduler/scheduler.go:769-803) for `jobs` jobs at once — the jobs of many
+ * what-if replicas back to back: duration accounting by job status and, when `tiresias` is set
+ * (s.Algorithm is "Tiresias" or "ElasticTiresias"), the demote / promote rules
+ * (pkg/algorithm/tiresias.go:27-36 thresholds and knob, :109-119 helpers).  Durations are
+ * time.Duration values: int64 nanoseconds.  Arrays marked io are updated in place.
+ * voda_compare_results replaces Scheduler.compareResults (scheduler.go:448-480): per job the
+ * action the scheduler takes when its GPU count goes from old_gpu to new_gpu.
+ */
+#define VODA_JOB_SUBMITTED 0 /* types.JobSubmitted .. JobFailed, pkg/common/types/types.go:34-46 */
+#define VODA_JOB_WAITING 1
+#define VODA_JOB_RUNNING 2
+#define VODA_JOB_COMPLETED 3
+#define VODA_JOB_FAILED 4
+
+#define VODA_ACT_NONE 0
+#define VODA_ACT_HALT 1      /* halts     (n > new, new == 0, job not completed / failed) */
+#define VODA_ACT_SCALE_IN 2  /* scaleIns  (n > new > 0) */
+#define VODA_ACT_SCALE_OUT 3 /* scaleOuts (0 < n < new) */
+#define VODA_ACT_START 4     /* starts    (n == 0 < new) */
+
+#define VODA_TICK_MAX_QUEUES 8
+
+typedef struct {
+  int32_t jobs;
+  int32_t tiresias;          /* 0 / 1 */
+  int32_t queue_num;         /* TiresiasQueueNum (2); <= VODA_TICK_MAX_QUEUES */
+  int32_t promote_knob;      /* TiresiasPromoteKnob (8) */
+  int64_t now_ns;            /* time.Now() of this tick, unix nanoseconds */
+  double thresholds_sec[VODA_TICK_MAX_QUEUES]; /* TiresiasThresholdsSec[0 .. queue_num-1] */
+  const int32_t* status;     /* [jobs] VODA_JOB_* */
+  const int32_t* num_gpu;    /* [jobs] s.JobNumGPU[job] */
+  int32_t* priority;         /* io [jobs] */
+  int64_t* last_update_ns;   /* io [jobs] Metrics.LastUpdateTime */
+  int64_t* running_ns;       /* io RunningDuration */
+  int64_t* gpu_ns;           /* io GpuDuration */
+  int64_t* total_ns;         /* io TotalDuration */
+  int64_t* waiting_ns;       /* io WaitingDuration */
+  int64_t* last_running_ns;  /* io LastRunningDuration */
+  int64_t* last_gpu_ns;      /* io LastGpuDuration */
+  int64_t* last_waiting_ns;  /* io LastWaitingDuration */
+  int32_t* changed;          /* out [jobs]: 1 where the job sets priorityChanged */
+} voda_tick_batch;
+
+/* device pointers; asynchronous on the context's stream */
+int voda_tick_dev(voda_ctx* ctx, const voda_tick_batch* dev_batch);
+int voda_compare_results_dev(voda_ctx* ctx, int32_t jobs, const int32_t* d_old_gpu, const int32_t* d_new_gpu,
+                             const int32_t* d_status, int32_t* d_action);
+/* host pointers (staged through the context; returns when the outputs are in place) */
+int voda_tick(voda_ctx* ctx, const voda_tick_batch* host_batch);
+int voda_compare_results(voda_ctx* ctx, int32_t jobs, const int32_t* old_gpu, const int32_t* new_gpu,
+                         const int32_t* status, int32_t* action);
+
 #ifdef __cplusplus
 }
 #endif

@@ -60,6 +60,20 @@ class CurveBatchStruct(C.Structure):  # voda_curve_batch
                 ("epoch_time_sec", C.c_void_p)]
 
 
+TICK_MAX_QUEUES = 8
+JOB_SUBMITTED, JOB_WAITING, JOB_RUNNING, JOB_COMPLETED, JOB_FAILED = range(5)
+ACT_NONE, ACT_HALT, ACT_SCALE_IN, ACT_SCALE_OUT, ACT_START = range(5)
+
+
+class TickBatchStruct(C.Structure):  # voda_tick_batch
+    _fields_ = [("jobs", C.c_int32), ("tiresias", C.c_int32), ("queue_num", C.c_int32), ("promote_knob", C.c_int32),
+                ("now_ns", C.c_int64), ("thresholds_sec", C.c_double * TICK_MAX_QUEUES),
+                ("status", C.c_void_p), ("num_gpu", C.c_void_p), ("priority", C.c_void_p),
+                ("last_update_ns", C.c_void_p), ("running_ns", C.c_void_p), ("gpu_ns", C.c_void_p),
+                ("total_ns", C.c_void_p), ("waiting_ns", C.c_void_p), ("last_running_ns", C.c_void_p),
+                ("last_gpu_ns", C.c_void_p), ("last_waiting_ns", C.c_void_p), ("changed", C.c_void_p)]
+
+
 PROTOTYPES = {
     "voda_ctx_create": (C.c_int, [C.c_int, C.POINTER(C.c_void_p)]),
     "voda_ctx_destroy": (None, [C.c_void_p]),
@@ -82,6 +96,10 @@ PROTOTYPES = {
     "voda_munkres_max_dev": (C.c_int, [C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     "voda_place": (C.c_int, [C.c_void_p, C.POINTER(PlaceBatchStruct), C.POINTER(PlaceOutStruct)]),
     "voda_place_dev": (C.c_int, [C.c_void_p, C.POINTER(PlaceBatchStruct), C.POINTER(PlaceOutStruct)]),
+    "voda_tick": (C.c_int, [C.c_void_p, C.POINTER(TickBatchStruct)]),
+    "voda_tick_dev": (C.c_int, [C.c_void_p, C.POINTER(TickBatchStruct)]),
+    "voda_compare_results": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "voda_compare_results_dev": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "voda_build_curves": (C.c_int, [C.c_void_p, C.POINTER(CurveBatchStruct), C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p]),
     "voda_build_curves_dev": (C.c_int, [C.c_void_p, C.POINTER(CurveBatchStruct), C.c_void_p, C.c_void_p, C.c_void_p,

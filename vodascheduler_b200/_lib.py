@@ -151,6 +151,38 @@ class Context:
                                                 st.ctypes.data), "voda_build_curves")
         return et[:jobs], sp[:jobs], ef[:jobs], st[:jobs]
 
+    # -- scheduler bookkeeping ---------------------------------------------------------
+    TICK_FIELDS = ("last_update_ns", "running_ns", "gpu_ns", "total_ns", "waiting_ns", "last_running_ns",
+                   "last_gpu_ns", "last_waiting_ns")
+
+    def tick(self, state: dict, now_ns: int, tiresias: bool, thresholds_sec=(3600.0, float("inf")), promote_knob=8):
+        """Scheduler.updateTimeMetrics for all jobs of `state` (dict of numpy arrays: status, num_gpu,
+        priority int32; TICK_FIELDS int64 nanoseconds), updated in place; returns `changed` [jobs]."""
+        n = int(state["status"].size)
+        for k in ("status", "num_gpu", "priority"):
+            state[k] = np.ascontiguousarray(state[k], np.int32)
+        for k in self.TICK_FIELDS:
+            state[k] = np.ascontiguousarray(state[k], np.int64)
+        changed = np.zeros(max(1, n), np.int32)
+        s = _abi.TickBatchStruct()
+        s.jobs, s.tiresias, s.queue_num, s.promote_knob, s.now_ns = n, int(bool(tiresias)), len(thresholds_sec), promote_knob, now_ns
+        for q, v in enumerate(thresholds_sec):
+            s.thresholds_sec[q] = v
+        for k in ("status", "num_gpu", "priority") + self.TICK_FIELDS:
+            setattr(s, k, state[k].ctypes.data)
+        s.changed = changed.ctypes.data
+        self._check(self._lib.voda_tick(self._h, C.byref(s)), "voda_tick")
+        return changed[:n]
+
+    def compare_results(self, old_gpu, new_gpu, status):
+        """Scheduler.compareResults: per job ACT_NONE / HALT / SCALE_IN / SCALE_OUT / START."""
+        old_gpu, new_gpu, status = (np.ascontiguousarray(x, np.int32) for x in (old_gpu, new_gpu, status))
+        n = int(old_gpu.size)
+        act = np.zeros(max(1, n), np.int32)
+        self._check(self._lib.voda_compare_results(self._h, n, old_gpu.ctypes.data, new_gpu.ctypes.data,
+                                                   status.ctypes.data, act.ctypes.data), "voda_compare_results")
+        return act[:n]
+
     # -- pinned host memory ------------------------------------------------------------
     def pinned(self, shape, dtype):
         """numpy array backed by voda_host_alloc (page-locked) memory."""

@@ -685,4 +685,125 @@ int voda_build_curves(voda_ctx* ctx, const voda_curve_batch* b, double* out_time
   return VODA_OK;
 }
 
+static int check_tick(voda_ctx* ctx, const voda_tick_batch* b) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  if (!b) return fail(ctx, VODA_E_INVALID, "null batch");
+  if (b->jobs < 0) return fail(ctx, VODA_E_INVALID, "negative job count");
+  if (b->queue_num < 0 || b->queue_num > VODA_TICK_MAX_QUEUES)
+    return fail(ctx, VODA_E_UNSUPPORTED, "tick: queue_num outside [0, VODA_TICK_MAX_QUEUES]");
+  if (b->jobs > 0 && (!b->status || !b->num_gpu || !b->priority || !b->last_update_ns || !b->running_ns || !b->gpu_ns ||
+                      !b->total_ns || !b->waiting_ns || !b->last_running_ns || !b->last_gpu_ns || !b->last_waiting_ns ||
+                      !b->changed))
+    return fail(ctx, VODA_E_INVALID, "tick: null array");
+  return VODA_OK;
+}
+
+static TickArgs tick_args(const voda_tick_batch* b) {
+  TickArgs a{};
+  a.jobs = b->jobs;
+  a.tiresias = b->tiresias;
+  a.queue_num = b->queue_num;
+  a.promote_knob = b->promote_knob;
+  a.now_ns = b->now_ns;
+  for (int q = 0; q < VODA_TICK_MAX_QUEUES; q++) a.thr[q] = b->thresholds_sec[q];
+  a.status = b->status;
+  a.num_gpu = b->num_gpu;
+  a.priority = b->priority;
+  a.last_update_ns = (long long*)b->last_update_ns;
+  a.running_ns = (long long*)b->running_ns;
+  a.gpu_ns = (long long*)b->gpu_ns;
+  a.total_ns = (long long*)b->total_ns;
+  a.waiting_ns = (long long*)b->waiting_ns;
+  a.last_running_ns = (long long*)b->last_running_ns;
+  a.last_gpu_ns = (long long*)b->last_gpu_ns;
+  a.last_waiting_ns = (long long*)b->last_waiting_ns;
+  a.changed = b->changed;
+  return a;
+}
+
+int voda_tick_dev(voda_ctx* ctx, const voda_tick_batch* b) {
+  int rc = check_tick(ctx, b);
+  if (rc || b->jobs == 0) return rc;
+  CU(cudaSetDevice(ctx->device));
+  CU(launch_tick(tick_args(b), ctx->stream));
+  ctx->launches += 1;
+  return VODA_OK;
+}
+
+int voda_tick(voda_ctx* ctx, const voda_tick_batch* b) {
+  int rc = check_tick(ctx, b);
+  if (rc || b->jobs == 0) return rc;
+  CU(cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->pipe[0];
+  const size_t J = (size_t)b->jobs, a4 = align256(4 * J), a8 = align256(8 * J);
+  rc = ensure(ctx, ctx->stage[0], 4 * a4 + 8 * a8, s);
+  if (rc) return rc;
+  char* base = (char*)ctx->stage[0].p;
+  int32_t* d4[4];
+  for (int i = 0; i < 4; i++) d4[i] = (int32_t*)(base + i * a4);
+  int64_t* d8[8];
+  for (int i = 0; i < 8; i++) d8[i] = (int64_t*)(base + 4 * a4 + i * a8);
+  int64_t* h8[8] = {b->last_update_ns, b->running_ns, b->gpu_ns, b->total_ns, b->waiting_ns, b->last_running_ns,
+                    b->last_gpu_ns, b->last_waiting_ns};
+  CU(cudaMemcpyAsync(d4[0], b->status, 4 * J, cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(d4[1], b->num_gpu, 4 * J, cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(d4[2], b->priority, 4 * J, cudaMemcpyHostToDevice, s));
+  for (int i = 0; i < 8; i++) CU(cudaMemcpyAsync(d8[i], h8[i], 8 * J, cudaMemcpyHostToDevice, s));
+  voda_tick_batch d = *b;
+  d.status = d4[0];
+  d.num_gpu = d4[1];
+  d.priority = d4[2];
+  d.changed = d4[3];
+  d.last_update_ns = d8[0];
+  d.running_ns = d8[1];
+  d.gpu_ns = d8[2];
+  d.total_ns = d8[3];
+  d.waiting_ns = d8[4];
+  d.last_running_ns = d8[5];
+  d.last_gpu_ns = d8[6];
+  d.last_waiting_ns = d8[7];
+  CU(launch_tick(tick_args(&d), s));
+  ctx->launches += 1;
+  CU(cudaMemcpyAsync(b->priority, d4[2], 4 * J, cudaMemcpyDeviceToHost, s));
+  CU(cudaMemcpyAsync(b->changed, d4[3], 4 * J, cudaMemcpyDeviceToHost, s));
+  for (int i = 0; i < 8; i++) CU(cudaMemcpyAsync(h8[i], d8[i], 8 * J, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  return VODA_OK;
+}
+
+int voda_compare_results_dev(voda_ctx* ctx, int32_t jobs, const int32_t* d_old, const int32_t* d_new,
+                             const int32_t* d_status, int32_t* d_action) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  if (jobs < 0) return fail(ctx, VODA_E_INVALID, "negative job count");
+  if (jobs == 0) return VODA_OK;
+  if (!d_old || !d_new || !d_status || !d_action) return fail(ctx, VODA_E_INVALID, "null buffer");
+  CU(cudaSetDevice(ctx->device));
+  CU(launch_compare(jobs, d_old, d_new, d_status, d_action, ctx->stream));
+  ctx->launches += 1;
+  return VODA_OK;
+}
+
+int voda_compare_results(voda_ctx* ctx, int32_t jobs, const int32_t* old_gpu, const int32_t* new_gpu,
+                         const int32_t* status, int32_t* action) {
+  if (!ctx) return fail(nullptr, VODA_E_INVALID, "null context");
+  if (jobs < 0) return fail(ctx, VODA_E_INVALID, "negative job count");
+  if (jobs == 0) return VODA_OK;
+  if (!old_gpu || !new_gpu || !status || !action) return fail(ctx, VODA_E_INVALID, "null buffer");
+  CU(cudaSetDevice(ctx->device));
+  cudaStream_t s = ctx->pipe[0];
+  const size_t J = (size_t)jobs, a4 = align256(4 * J);
+  int rc = ensure(ctx, ctx->stage[0], 4 * a4, s);
+  if (rc) return rc;
+  char* base = (char*)ctx->stage[0].p;
+  CU(cudaMemcpyAsync(base, old_gpu, 4 * J, cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(base + a4, new_gpu, 4 * J, cudaMemcpyHostToDevice, s));
+  CU(cudaMemcpyAsync(base + 2 * a4, status, 4 * J, cudaMemcpyHostToDevice, s));
+  CU(launch_compare(jobs, (const int32_t*)base, (const int32_t*)(base + a4), (const int32_t*)(base + 2 * a4),
+                    (int32_t*)(base + 3 * a4), s));
+  ctx->launches += 1;
+  CU(cudaMemcpyAsync(action, base + 3 * a4, 4 * J, cudaMemcpyDeviceToHost, s));
+  CU(cudaStreamSynchronize(s));
+  return VODA_OK;
+}
+
 }  // extern "C"

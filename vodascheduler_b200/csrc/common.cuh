@@ -64,6 +64,18 @@ struct PlaceArgs {
   int32_t* status;
 };
 
+struct TickArgs {  // voda_tick_batch with the thresholds by value
+  int jobs, tiresias, queue_num, promote_knob;
+  long long now_ns;
+  double thr[VODA_TICK_MAX_QUEUES];
+  const int32_t* status;
+  const int32_t* num_gpu;
+  int32_t* priority;
+  long long *last_update_ns, *running_ns, *gpu_ns, *total_ns, *waiting_ns, *last_running_ns, *last_gpu_ns,
+      *last_waiting_ns;
+  int32_t* changed;
+};
+
 __host__ __device__ inline int next_pow2(int x) {
   int p = 1;
   while (p < x) p <<= 1;

@@ -40,4 +40,9 @@ cudaError_t launch_curves(int jobs, const int32_t* rec_off, const int32_t* worke
                           double* out_time, double* out_speedup, double* out_eff, int32_t* out_status,
                           cudaStream_t stream);
 
+// scheduler bookkeeping (tick.cu)
+cudaError_t launch_tick(const TickArgs& a, cudaStream_t stream);
+cudaError_t launch_compare(int jobs, const int32_t* old_gpu, const int32_t* new_gpu, const int32_t* status,
+                           int32_t* action, cudaStream_t stream);
+
 }  // namespace voda
