@@ -147,16 +147,16 @@ int voda_allocate_dev(voda_ctx* ctx, const voda_alloc_batch* dev_batch,
  * no counterpart in the reference.  It computes exactly what voda_allocate_dev computes for
  * algo == VODA_ALGO_FFDL_OPTIMIZER (every pointer, inside the struct too, is a device pointer;
  * max_jobs and max_total_gpu must be declared; `algo` is ignored), but it never calls
- * cudaMalloc / cudaFree: the kernel's SOL scratch is a fixed 32 MiB array inside the library
+ * cudaMalloc / cudaFree: the kernels' scratch (stored rows of the DP table) is a fixed 32 MiB array inside the library
  * image (held by every GPU that loads the library until the process exits) instead of a
  * buffer the context grows on demand.  Use it when the GPU's memory already belongs to
  * someone else's allocator, or when the calling thread cannot afford the device-wide stall
  * of an allocation.  No voda_ctx is needed: it runs on the CURRENT device, on `stream`
  * (a cudaStream_t, NULL = default stream), asynchronously.
- *   - Shapes whose per-round scratch, min(max_jobs, max_total_gpu) * ceil(max_total_gpu/4) * 8
+ *   - Shapes whose per-round scratch, about min(max_jobs, max_total_gpu) * (ceil(max_total_gpu/8) * 32 + 4 * speedup_stride + 16)
  *     bytes, exceeds 32 MiB are refused with VODA_E_TOO_LARGE and a message in errbuf.
  *   - All calls on a GPU share the array (it keeps the previous call's bytes; nothing needs
- *     clearing because every SOL row is rewritten before it is read).  Calls that overlap on
+ *     clearing: the backtrack only uses what the same round's forward pass wrote).  Calls that overlap on
  *     the GPU race on it: serialise them.
  *   - The first call on each device looks up the array's device address; make that call
  *     before any stream capture on the device.

@@ -149,7 +149,7 @@ int dispatch_alloc(voda_ctx* ctx, const AllocArgs& a, DevBuf& scratch, cudaStrea
     case VODA_ALGO_FFDL_OPTIMIZER: {
       if (ffdl_smem_bytes(a) > 200 * 1024)
         return fail(ctx, VODA_E_UNSUPPORTED, "FfDL: total_gpu / jobs too large for one CTA's shared memory");
-      // every round keeps its SOL slab until the backtrack kernel has read it: cap the scratch
+      // every round keeps its slab of stored DP rows until the backtrack kernel has read it: cap the scratch
       // at 16 GiB and walk larger batches in sub-batches (two launches each)
       const size_t per = (ffdl_scratch_per_round(a) + 255) & ~(size_t)255;
       const size_t budget = (size_t)16 << 30;

@@ -1,8 +1,8 @@
 // noalloc.cu — voda_ffdl_allocate_static: the FfDL Optimizer batch kernel for callers that
 // must not allocate device memory.
 //
-// Who needs this.  voda_allocate_dev sizes its SOL scratch (the table of chosen g values the
-// DP writes and the backtrack reads) with cudaMalloc on first use and again whenever a bigger
+// Who needs this.  voda_allocate_dev sizes its scratch (the rows of the DP table the forward
+// pass stores and the backtrack reads back) with cudaMalloc on first use and again whenever a bigger
 // batch arrives.  Some hosts of this library cannot tolerate that:
 //   * a scheduler that shares the GPU with a training framework whose caching allocator has
 //     already claimed the HBM — a late cudaMalloc there simply fails;
@@ -18,12 +18,12 @@
 // pointers).
 //
 // Limits and sharing.  The array is 32 MiB.  One round needs a slab of about
-// min(max_jobs, max_total_gpu) * ceil(max_total_gpu / 4) * 8 bytes; the batch is walked in
+// min(max_jobs, max_total_gpu) * (ceil(max_total_gpu / 8) * 32 + 4 * W + 16) bytes; the batch is walked in
 // passes of as many rounds as fit (so it is slower than voda_allocate_dev on big batches),
 // and a batch whose single round does not fit is rejected with VODA_E_TOO_LARGE.  All calls on
 // a GPU share the one array and it keeps whatever the previous call left in it.  Nothing has
-// to start at zero: each DP row rewrites its whole SOL row before the backtrack reads any cell
-// of it, so no clearing is done.  Two calls that overlap on the GPU (different streams, or
+// to start at zero: the backtrack only uses cells, row records and S entries the forward pass of
+// the same round has written (what it loads beyond them is masked), so no clearing is done.  Two calls that overlap on the GPU (different streams, or
 // different host threads) would write the same slabs and race — serialise them.
 //
 // Set-up.  In host code the name `g_static_scratch` is only a stand-in for the device array,
@@ -115,7 +115,7 @@ extern "C" int voda_ffdl_allocate_static(void* stream, const voda_alloc_batch* b
   const size_t per = (ffdl_scratch_per_round(a) + 255) & ~(size_t)255;  // bytes one round needs
   if (per > VODA_STATIC_SCRATCH_BYTES) {
     char detail[160];
-    std::snprintf(detail, sizeof detail, "one round needs %zu bytes of SOL scratch, the fixed array holds %u", per,
+    std::snprintf(detail, sizeof detail, "one round needs %zu bytes of scratch, the fixed array holds %u", per,
                   (unsigned)VODA_STATIC_SCRATCH_BYTES);
     return report(errbuf, errbuf_len, VODA_E_TOO_LARGE, "batch shape exceeds the static scratch", detail);
   }
