@@ -60,6 +60,7 @@ constexpr int kCells = 8;  // adjacent cells per thread: two float4 groups, a th
 #endif
 constexpr int kCkpt = VODA_FFDL_CKPT;
 constexpr int kCkptGmax = 32;
+static_assert(kCkpt == 4, "ffdl_walk_sparse dispatches the topmost segment on 1..4 rows");
 constexpr int kBand = kCkpt * kCkptGmax;  // cells per band row
 constexpr int kBandPad = kCkptGmax;       // -inf cells in front of a band row (columns below 0)
 constexpr int kBandRow = kBandPad + kBand + 32;
@@ -503,9 +504,107 @@ __device__ __forceinline__ unsigned f32_key(float p) {
 // memory with the forward pass's own recurrence (same additions, a maximum: any order gives the
 // same value), and then takes the kCkpt walk steps from shared memory.  One dependent global
 // load per segment instead of one per row.
+// One segment of the checkpointed walk: the NR walk rows c+NR .. c+1 (NR = kCkpt except for the
+// topmost segment of a round), from position k; returns the position below the segment.
+template <int NR>
+__device__ __forceinline__ int ffdl_segment(const float* slab, const float* gsrows, const int4* grows, int32_t* out,
+                                            int SW, int W, int rowFloats, int lane, int slane, int c, int k,
+                                            float (*band)[kBandRow], float (*ssm)[32]) {
+  const unsigned full = 0xffffffffu;
+  const int4 none = make_int4(0, 0, 0, 0);
+  const unsigned keyFloor = f32_key(-10000.0f);
+  int4 rec[NR];    // rec[i]: row c+1+i
+  float sreg[NR];  // S_{c+1+i}[1 + lane]
+  const int4* recp = grows + c;
+  const float* sp = gsrows + c * SW + slane;
+#pragma unroll
+  for (int i = 0; i < NR; i++) {
+    rec[i] = recp[i];
+    sreg[i] = sp[i * SW];
+  }
+  const int4 recc = c >= 1 ? recp[-1] : none;  // the checkpoint row's klim and c
+  // the next segment's records and S rows do not depend on the position: pull them into L2
+  if (c >= kCkpt) {
+    if (lane == 0) prefetch_l2(recp - kCkpt - 1);
+    if (lane >= 1 && lane <= kCkpt) prefetch_l2(gsrows + (c - kCkpt + lane - 1) * SW);
+    // ... and so is the stretch of the next checkpoint row just below the current position
+    if (lane >= 8 && lane < 12 && c > kCkpt)
+      prefetch_l2(slab + (c - kCkpt - 1) * rowFloats + max(k - 1 - 32 * (lane - 8), 0));
+  }
+#pragma unroll
+  for (int i = 0; i < NR; i++) {
+    // S as the recurrence uses it: a g the table does not hold reads 0 (a Go map miss)
+    sreg[i] = lane + 1 <= W - 1 ? sreg[i] : 0.0f;
+    ssm[i][lane] = sreg[i];
+  }
+  int lo[NR];  // lo[i]: lowest column of row c+i the walk can read
+  {
+    int D = 0;
+#pragma unroll
+    for (int i = NR - 1; i >= 0; i--) {
+      D += max(0, rec[i].y);  // (0 past the segment)
+      lo[i] = max(0, k - D);
+    }
+  }
+  const int base = lo[0];
+  const int width = k - base;  // <= kBand: columns base .. k-1
+  // 1. the stored row c (or row 0 = 0)
+  {
+    const float* crow = slab + max(c - 1, 0) * rowFloats;  // P[c][x] at crow[x-1]
+    const float cC = __int_as_float(recc.w);
+    for (int idx = lane; idx < width; idx += 32) {
+      const int x = base + idx;
+      const float pv = crow[max(x, 1) - 1];
+      band[0][kBandPad + idx] = c == 0 ? 0.0f : (x == 0 ? -10000.0f : (x >= recc.z ? cC : pv));
+    }
+  }
+  __syncwarp();
+  // 2. rows c+1 .. c+NR-1
+#pragma unroll
+  for (int i = 1; i < NR; i++) {
+    {
+      const int gmax = rec[i - 1].y, klim = rec[i - 1].z;
+      const float cR = __int_as_float(rec[i - 1].w);
+      const float* sv = ssm[i - 1];
+      for (int idx0 = lo[i] - base; idx0 < width; idx0 += 32) {  // uniform trip count
+        const int idx = idx0 + lane;
+        const int x = base + idx;
+        // P[r-1][x-g] sits at prow[-g]; a column below 0 falls into the -inf pad (the stretch
+        // starts at column 0 whenever that can happen), so the k-g >= 0 test needs no branch
+        const float* prow = band[i - 1] + kBandPad + min(idx, width);
+        float best = -10000.0f;
+        int g = 1;
+        for (; g + 1 <= gmax; g += 2) best = fmaxf(fmaxf(best, sv[g - 1] + prow[-g]), sv[g] + prow[-g - 1]);
+        if (g <= gmax) best = fmaxf(best, sv[g - 1] + prow[-g]);
+        if (x == 0) best = -10000.0f;
+        else if (x >= klim) best = cR;
+        if (idx < width) band[i][kBandPad + idx] = best;
+      }
+      __syncwarp();
+    }
+  }
+  // 3. the walk steps c+NR .. c+1 (row c+1+i reads band row i)
+#pragma unroll
+  for (int i = NR - 1; i >= 0; i--) {
+    {
+      const int gm = min(rec[i].y, k);  // candidates g = 1 .. gm (k-g >= 0); gm <= 32 in a sparse round
+      const int g = 1 + lane;
+      const float sg = sreg[i];
+      const float pg = g <= gm ? band[i][kBandPad + k - g - base] : 0.0f;
+      const float p = sg + pg;
+      const unsigned key = (g <= gm && p == p) ? f32_key(p) : 0u;
+      const unsigned top = __reduce_max_sync(full, key);
+      const int sol = top > keyFloor ? __ffs((int)__ballot_sync(full, key == top)) : 0;
+      if (lane == 0) out[rec[i].x] = sol;
+      k -= sol;
+    }
+  }
+  __syncwarp();
+  return k;
+}
+
 __device__ __forceinline__ void ffdl_walk_sparse(const AllocArgs& a, const FfdlScratch& sc, int rr, int o, int J, int K,
                                                  int lane, float (*band)[kBandRow], float (*ssm)[32]) {
-  const unsigned full = 0xffffffffu;
   const float* slab = sc.P + (size_t)rr * sc.slabFloats;
   const float* gsrows = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)sc.SW;
   const int4* grows = reinterpret_cast<const int4*>(sc.rows + (size_t)rr * (size_t)sc.Jcap);  // job, gmax, klim, c
@@ -514,102 +613,17 @@ __device__ __forceinline__ void ffdl_walk_sparse(const AllocArgs& a, const FfdlS
   const int W = a.stride;
   const int rowFloats = (int)sc.rowFloats;
   const int slane = min(lane, SW - 1);
-  const int4 none = make_int4(0, 0, 0, 0);
-  const unsigned keyFloor = f32_key(-10000.0f);
   int k = K;
-  for (int jTop = J; jTop >= 1;) {
-    const int c = ((jTop - 1) / kCkpt) * kCkpt;  // rows c .. jTop-1 feed the walk rows jTop .. c+1
-    const int nr = jTop - c;                     // 1 .. kCkpt
-    int4 rec[kCkpt];    // rec[i]: row c+1+i
-    float sreg[kCkpt];  // S_{c+1+i}[1 + lane]
-    const int4* recp = grows + c;
-    const float* sp = gsrows + c * SW + slane;
-#pragma unroll
-    for (int i = 0; i < kCkpt; i++) {  // (past the segment the loads stay inside the scratch and are masked)
-      rec[i] = recp[i];
-      sreg[i] = sp[i * SW];
-    }
-    const int4 recc = c >= 1 ? recp[-1] : none;  // the checkpoint row's klim and c
-    // the next segment's records and S rows do not depend on the position: pull them into L2
-    if (c >= kCkpt) {
-      if (lane == 0) prefetch_l2(recp - kCkpt - 1);
-      if (lane >= 1 && lane <= kCkpt) prefetch_l2(gsrows + (c - kCkpt + lane - 1) * SW);
-      // ... and so is the stretch of the next checkpoint row just below the current position
-      if (lane >= 8 && lane < 12 && c > kCkpt)
-        prefetch_l2(slab + (c - kCkpt - 1) * rowFloats + max(k - 1 - 32 * (lane - 8), 0));
-    }
-#pragma unroll
-    for (int i = 0; i < kCkpt; i++) {
-      if (i >= nr) rec[i].y = 0;
-      // S as the recurrence uses it: a g the table does not hold reads 0 (a Go map miss)
-      sreg[i] = lane + 1 <= W - 1 ? sreg[i] : 0.0f;
-      ssm[i][lane] = sreg[i];
-    }
-    int lo[kCkpt];  // lo[i]: lowest column of row c+i the walk can read
-    {
-      int D = 0;
-#pragma unroll
-      for (int i = kCkpt - 1; i >= 0; i--) {
-        D += max(0, rec[i].y);  // (0 past the segment)
-        lo[i] = max(0, k - D);
-      }
-    }
-    const int base = lo[0];
-    const int width = k - base;  // <= kBand: columns base .. k-1
-    // 1. the stored row c (or row 0 = 0)
-    {
-      const float* crow = slab + max(c - 1, 0) * rowFloats;  // P[c][x] at crow[x-1]
-      const float cC = __int_as_float(recc.w);
-      for (int idx = lane; idx < width; idx += 32) {
-        const int x = base + idx;
-        const float pv = crow[max(x, 1) - 1];
-        band[0][kBandPad + idx] = c == 0 ? 0.0f : (x == 0 ? -10000.0f : (x >= recc.z ? cC : pv));
-      }
-    }
-    __syncwarp();
-    // 2. rows c+1 .. jTop-1
-#pragma unroll
-    for (int i = 1; i < kCkpt; i++) {
-      if (i < nr) {
-        const int gmax = rec[i - 1].y, klim = rec[i - 1].z;
-        const float cR = __int_as_float(rec[i - 1].w);
-        const float* sv = ssm[i - 1];
-        for (int idx0 = lo[i] - base; idx0 < width; idx0 += 32) {  // uniform trip count
-          const int idx = idx0 + lane;
-          const int x = base + idx;
-          // P[r-1][x-g] sits at prow[-g]; a column below 0 falls into the -inf pad (the stretch
-          // starts at column 0 whenever that can happen), so the k-g >= 0 test needs no branch
-          const float* prow = band[i - 1] + kBandPad + min(idx, width);
-          float best = -10000.0f;
-          int g = 1;
-          for (; g + 1 <= gmax; g += 2) best = fmaxf(fmaxf(best, sv[g - 1] + prow[-g]), sv[g] + prow[-g - 1]);
-          if (g <= gmax) best = fmaxf(best, sv[g - 1] + prow[-g]);
-          if (x == 0) best = -10000.0f;
-          else if (x >= klim) best = cR;
-          if (idx < width) band[i][kBandPad + idx] = best;
-        }
-        __syncwarp();
-      }
-    }
-    // 3. the walk steps jTop .. c+1 (row c+1+i reads band row i)
-#pragma unroll
-    for (int i = kCkpt - 1; i >= 0; i--) {
-      if (i < nr) {
-        const int gm = min(rec[i].y, k);  // candidates g = 1 .. gm (k-g >= 0); gm <= 32 in a sparse round
-        const int g = 1 + lane;
-        const float sg = sreg[i];
-        const float pg = g <= gm ? band[i][kBandPad + k - g - base] : 0.0f;
-        const float p = sg + pg;
-        const unsigned key = (g <= gm && p == p) ? f32_key(p) : 0u;
-        const unsigned top = __reduce_max_sync(full, key);
-        const int sol = top > keyFloor ? __ffs((int)__ballot_sync(full, key == top)) : 0;
-        if (lane == 0) out[rec[i].x] = sol;
-        k -= sol;
-      }
-    }
-    __syncwarp();
-    jTop = c;
+  // the topmost segment takes the rows above the highest multiple of kCkpt; the others are full
+  int c = ((J - 1) / kCkpt) * kCkpt;
+  switch (J - c) {
+    case 1: k = ffdl_segment<1>(slab, gsrows, grows, out, SW, W, rowFloats, lane, slane, c, k, band, ssm); break;
+    case 2: k = ffdl_segment<2>(slab, gsrows, grows, out, SW, W, rowFloats, lane, slane, c, k, band, ssm); break;
+    case 3: k = ffdl_segment<3>(slab, gsrows, grows, out, SW, W, rowFloats, lane, slane, c, k, band, ssm); break;
+    default: k = ffdl_segment<kCkpt>(slab, gsrows, grows, out, SW, W, rowFloats, lane, slane, c, k, band, ssm); break;
   }
+  for (c -= kCkpt; c >= 0; c -= kCkpt)
+    k = ffdl_segment<kCkpt>(slab, gsrows, grows, out, SW, W, rowFloats, lane, slane, c, k, band, ssm);
 }
 
 // The walk of a round that stored every row of P (some job can take more than kCkptGmax GPUs):
