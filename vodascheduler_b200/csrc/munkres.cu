@@ -33,7 +33,10 @@ __device__ __forceinline__ long long warp_max_ll(long long v) {
 }
 
 template <typename CellT>
-__global__ void __launch_bounds__(32) munkres_kernel(int n, int batch, const int64_t* __restrict__ A,
+#ifndef VODA_MK_MINBLOCKS
+#define VODA_MK_MINBLOCKS 32  // 64 registers: all 32 one-warp CTAs of an SM resident (74 registers held 27: 8.1 -> 6.1 ms per 20k matrices)
+#endif
+__global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, int batch, const int64_t* __restrict__ A,
                                                      int32_t* __restrict__ out, int32_t* __restrict__ status,
                                                      unsigned char* __restrict__ need, int level,
                                                      unsigned char* __restrict__ slabs, size_t slabBytes) {
