@@ -45,7 +45,9 @@ extern "C" {
 #define VODA_ST_EXCEEDED_TOTAL  4  /* "Invalid GPU allocations: exceeded total GPUs"    utils.go:40-42 */
 #define VODA_ST_INFEASIBLE      5  /* "infeasible"                              ffdl_optimizer.go:109-114 */
 #define VODA_ST_NOT_FOUND       6  /* "Not found"                  types.go:45, elastic_tiresias.go:188-189 */
-#define VODA_ST_NONTERMINATING  7  /* guard: the reference loop would never end (bestFit, placement_manager.go:437-485) */
+#define VODA_ST_NONTERMINATING  7  /* guard: the reference loop would never end (bestFit, placement_manager.go:437-485;
+                                      ElasticTiresias greedy loop with MinNumProc == 0, elastic_tiresias.go:136-143:
+                                      the pick changes neither the job's count nor the free GPUs nor its gain) */
 #define VODA_ST_BOUND           8  /* round exceeds the max_jobs / max_total_gpu the caller declared */
 #define VODA_ST_RUNTIME_PANIC   9  /* the Go runtime itself would panic (makeslice with negative total) */
 
@@ -72,6 +74,9 @@ void* voda_ctx_stream(voda_ctx* ctx);
 int  voda_ctx_sync(voda_ctx* ctx);
 /* Number of kernels of this library launched through the context since it was created. */
 int64_t voda_ctx_launch_count(voda_ctx* ctx);
+/* Bytes the LAST host-pointer call on this context (voda_allocate, voda_munkres_max) copied host->device and
+ * device->host — what actually crossed PCIe, e.g. only the speedup columns the policy can index. */
+void voda_ctx_copied_bytes(voda_ctx* ctx, int64_t* h2d_bytes, int64_t* d2h_bytes);
 const char* voda_last_error(voda_ctx* ctx);
 const char* voda_status_str(int32_t status);
 const char* voda_version(void);

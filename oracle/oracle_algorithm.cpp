@@ -14,6 +14,7 @@
 // Build: g++ -O2 -fno-fast-math -ffp-contract=off (no FMA contraction: Go on amd64 rounds
 // every float32 operation separately).
 
+#include <cstring>
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -275,9 +276,15 @@ void ElasticTiresias_Schedule(ReadyJobs& jobs, long totalGPU, Result& result, lo
     if (gain[job.Name] <= 0) break;
     if (result[job.Name] == 0) {
       if (freeGPU >= job.Config.MinNumProc) {
+        const float before = gain[job.Name];
         result[job.Name] = job.Config.MinNumProc;
         freeGPU -= job.Config.MinNumProc;
         gain[job.Name] = calNextGain(job.Info->Speedup, result[job.Name]);
+        // NOT in the reference: with MinNumProc == 0 this branch changes nothing but the gain;
+        // once the gain repeats, the Go loop never ends.  Reported as a status instead.
+        const float after = gain[job.Name];
+        if (job.Config.MinNumProc == 0 && std::memcmp(&before, &after, 4) == 0 && !(after <= 0))
+          throw Panic{VODA_ST_NONTERMINATING};
       } else {
         removeAt(jobs, indexOf(jobs, job.Name));
       }

@@ -9,6 +9,7 @@
 // bench.py prints beside the structure-faithful timing.  Reference file:line citations are
 // on each function; paths are relative to the reference tree.
 
+#include <cstring>
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -136,6 +137,13 @@ int tiresias(const Round& R, std::vector<long>& r, long Q) {
 // (Q5): the head of the doubly stable-sorted list equals the maximum of
 // (gain desc, Priority asc, stamp desc), stamp = -(position in the pruned list) at first and
 // the pick number once a job has been picked.
+bool sameBits(float a, float b) {
+  uint32_t x, y;
+  std::memcpy(&x, &a, 4);
+  std::memcpy(&y, &b, 4);
+  return x == y;
+}
+
 int elasticTiresias(const Round& R, std::vector<long>& r, long Q, long compaction) {
   const int n = R.n;
   std::vector<float> gain((size_t)n);
@@ -181,9 +189,14 @@ int elasticTiresias(const Round& R, std::vector<long>& r, long Q, long compactio
     if (gain[(size_t)best] <= 0) break;
     if (r[(size_t)best] == 0) {
       if (free >= R.mn(best)) {
+        const float before = gain[(size_t)best];
         r[(size_t)best] = R.mn(best); free -= R.mn(best);
         gain[(size_t)best] = R.S(best, r[(size_t)best] + 1) - R.S(best, r[(size_t)best]);
         stamp[(size_t)best] = it;
+        // MinNumProc == 0: nothing changed but (possibly) the gain; if that is unchanged too the
+        // reference repeats this pick forever (guard, same rule as the kernel's)
+        if (R.mn(best) == 0 && sameBits(before, gain[(size_t)best]) && !(gain[(size_t)best] <= 0))
+          return VODA_ST_NONTERMINATING;
       } else { live[(size_t)best] = 0; nlive--; }
     } else {
       r[(size_t)best] += 1; free -= 1;

@@ -31,6 +31,12 @@ tir = [job("A", first=5, prio=0, np_=2, mn=1, mx=4, curve=C), job("B", first=3, 
 ffdl3 = [job("A", submit=1, mn=1, mx=4, curve=C), job("B", submit=2, mn=1, mx=4, curve=D),
          job("C", submit=3, mn=1, mx=6, curve=C)]
 ffdl2 = [job("A", submit=1, mn=1, mx=4), job("B", submit=2, mn=1, mx=4)]
+# MinNumProc == 0 (S[0] = 0.5 so that the first gain S[0]/0 is +Inf, not NaN).  Hand trace, total 3:
+# basic portion A(np 5) does not fit, B gets 1 (free 2, gain S[2]-S[1] = 1); greedy: A (+Inf) takes its
+# minimum 0 -> r 0, free 2, gain S[1]-S[0] = 0.5; B (1) -> 2 = max, removed, free 1; A (0.5) takes 0
+# again -> r, free, gain all unchanged: the Go loop repeats this pick forever -> guard status 7.
+E = [0.5, 1, 1.9, 2.7, 3.4]
+tir_min0 = [job("A", first=1, prio=0, np_=5, mn=0, mx=4, curve=E), job("B", first=2, prio=0, np_=1, mn=1, mx=2)]
 afsl3 = [job("A", submit=1, mn=1, mx=4, rem=100, curve=C), job("B", submit=2, mn=1, mx=4, rem=50, curve=D),
          job("C", submit=3, mn=1, mx=6, rem=200, curve=C)]
 
@@ -43,6 +49,7 @@ alloc = [
     dict(kat="5", algo="ElasticTiresias", jobs=tir, total=8, status=OK, expect=dict(A=2, B=1, C=4, D=1)),
     dict(kat="6", algo="ElasticTiresias", jobs=tir, total=12, status=OK, expect=dict(A=4, B=2, C=4, D=2)),
     dict(kat="7", algo="ElasticTiresias", jobs=tir, total=5, status=OK, expect=dict(A=0, B=0, C=4, D=1)),
+    dict(kat="15", algo="ElasticTiresias", jobs=tir_min0, total=3, status=NONTERM, expect=None),
     dict(kat="8", algo="FfDLOptimizer", jobs=ffdl3, total=8, status=OK, expect=dict(A=4, B=1, C=3)),
     dict(kat="9", algo="FfDLOptimizer", jobs=ffdl3, total=2, status=OK, expect=dict(A=1, B=1, C=0)),
     dict(kat="10", algo="FfDLOptimizer", jobs=ffdl2, total=6, status=OK, expect=dict(A=4, B=2)),

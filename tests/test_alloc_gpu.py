@@ -52,6 +52,16 @@ def test_quirks(ctx, oracle, algo):
 
 
 @pytest.mark.parametrize("algo", ALGOS)
+def test_min_zero(ctx, oracle, algo):
+    """MinNumProc == 0 (what a JSON request without min_num_proc decodes to): the reference's
+    ElasticTiresias loop never ends on such a job; the kernel must return, with status 7."""
+    b = synth.min_zero_batch(algo, rounds=400, jobs_per_round=40, total_gpu=64)
+    g, s = _same(ctx, oracle, b)
+    if algo == "ElasticTiresias":
+        assert (s == 7).any()
+
+
+@pytest.mark.parametrize("algo", ALGOS)
 @pytest.mark.parametrize("jobs,total", [(1, 1), (3, 0), (7, 3), (33, 31), (64, 16), (129, 257), (300, 1000)])
 def test_shapes(ctx, oracle, algo, jobs, total):
     b = synth.jobs_batch(algo, rounds=24, jobs_per_round=jobs, total_gpu=total)

@@ -30,6 +30,19 @@ def test_faithful_equals_dense_quirks(oracle, algo):
 
 
 @pytest.mark.parametrize("algo", ALGO_NAMES)
+def test_faithful_equals_dense_min_zero(oracle, algo):
+    """MinNumProc == 0: ElasticTiresias reaches the pick that changes nothing (the Go loop never
+    ends there); both restatements cut it at the same moment with status 7."""
+    b = synth.min_zero_batch(algo, rounds=120, jobs_per_round=24, total_gpu=40)
+    g0, s0 = oracle.allocate(b, threads=2)
+    g1, s1 = oracle.allocate(b, dense=True)
+    assert np.array_equal(s0, s1)
+    assert np.array_equal(g0, g1)
+    if algo == "ElasticTiresias":
+        assert (s0 == 7).any() and (s0 == 0).any()
+
+
+@pytest.mark.parametrize("algo", ALGO_NAMES)
 def test_validate_invariants(oracle, algo):
     """Rounds with status 0 satisfy what validateResult (utils.go:18-42) checks."""
     b = synth.quirk_batch(algo, rounds=100, jobs_per_round=30, total_gpu=64)

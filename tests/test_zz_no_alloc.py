@@ -37,20 +37,27 @@ def _run_both(ctx, lib, batch):
     return ref_g.cpu().numpy(), ref_s.cpu().numpy(), got_g.cpu().numpy(), got_s.cpu().numpy()
 
 
-def test_static_scratch_matches_allocating_entry_point_twice():
-    """Two calls in a row (different batches, so the second one finds the first one's bytes in
-    the shared array) both equal voda_allocate_dev bit for bit — allocations and statuses."""
+def test_static_scratch_matches_allocating_entry_point_twice(oracle):
+    """Calls in a row on different batches (each finds the previous one's bytes in the shared
+    array; the third uses a much smaller layout, so stale rows of the larger ones lie under its
+    slabs) all equal voda_allocate_dev bit for bit — allocations and statuses — and, so that a
+    defect common to both GPU entry points cannot pass, the CPU oracle as well."""
     from vodascheduler_b200 import Context
     ctx = Context(0)
     try:
         lib = ctx._lib
         first = synth.jobs_batch("FfDLOptimizer", rounds=300, jobs_per_round=96, total_gpu=320, ragged=True)
         second = synth.quirk_batch("FfDLOptimizer", rounds=500, jobs_per_round=48, total_gpu=200, seed=99)
-        for batch in (first, second):
+        third = synth.jobs_batch("FfDLOptimizer", rounds=40, jobs_per_round=7, total_gpu=12, ragged=True, seed=5)
+        for batch in (first, second, third):
             ref_g, ref_s, got_g, got_s = _run_both(ctx, lib, batch)
             assert np.array_equal(got_s, ref_s)
             assert np.array_equal(got_g, ref_g)
-        assert (ref_s != 0).any()  # the second batch exercises the panic statuses too
+            cpu_g, cpu_s = oracle.allocate(batch, dense=True, threads=8)
+            assert np.array_equal(got_s, cpu_s)
+            assert np.array_equal(got_g, cpu_g)
+            if batch is second:
+                assert (ref_s != 0).any()  # the quirk batch exercises the panic statuses too
     finally:
         ctx.close()
 

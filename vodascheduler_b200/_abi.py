@@ -80,6 +80,7 @@ PROTOTYPES = {
     "voda_ctx_stream": (C.c_void_p, [C.c_void_p]),
     "voda_ctx_sync": (C.c_int, [C.c_void_p]),
     "voda_ctx_launch_count": (C.c_int64, [C.c_void_p]),
+    "voda_ctx_copied_bytes": (None, [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "voda_last_error": (C.c_char_p, [C.c_void_p]),
     "voda_status_str": (C.c_char_p, [C.c_int32]),
     "voda_version": (C.c_char_p, []),

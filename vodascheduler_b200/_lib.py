@@ -63,9 +63,14 @@ class Context:
 
     # -- plumbing ----------------------------------------------------------------------
     def close(self):
+        """Destroys the context and frees the page-locked memory handed out by pinned() /
+        pin_batch(): arrays returned by those die with the context."""
         if getattr(self, "_h", None):
             self._lib.voda_ctx_destroy(self._h)
             self._h = None
+            for p in getattr(self, "_pins", []):
+                self._lib.voda_host_free(p)
+            self._pins = []
 
     def __del__(self):
         try:
@@ -88,6 +93,13 @@ class Context:
     @property
     def launches(self):
         return int(self._lib.voda_ctx_launch_count(self._h))
+
+    @property
+    def copied_bytes(self):
+        """(host->device, device->host) bytes of the last host-pointer call."""
+        a, b = C.c_int64(0), C.c_int64(0)
+        self._lib.voda_ctx_copied_bytes(self._h, C.byref(a), C.byref(b))
+        return int(a.value), int(b.value)
 
     # -- allocation --------------------------------------------------------------------
     def allocate(self, batch: AllocBatch, out_gpus=None, out_status=None):

@@ -6,6 +6,7 @@
 // enqueue kernels on the context's main stream.  Nothing here computes scheduling results on
 // the CPU; without a CUDA device voda_ctx_create fails and no other entry point can be used.
 #include <algorithm>
+#include <climits>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -38,7 +39,9 @@ struct voda_ctx {
   cudaEvent_t h2d_done[2] = {nullptr, nullptr};  // the slot's host staging has been consumed
   std::unique_ptr<HostPool> pool;  // host threads that pack rows (created on first use)
   bool pack_rows = false;          // VODA_PACK_ROWS=1 enables the FfDL row packing (measured slower: DESIGN.md)
+  bool narrow_cols = true;         // VODA_NARROW_COLS=0: always ship the full-width speedup table
   int64_t launches = 0;
+  int64_t h2d_bytes = 0, d2h_bytes = 0;  // bytes the last host-pointer call copied
   std::string err;
 };
 
@@ -79,6 +82,20 @@ int ensure(voda_ctx* ctx, DevBuf& b, size_t bytes, cudaStream_t user) {
 
 inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
+// Host-pointer entry points enqueue copies and kernels that write into the CALLER's buffers.  If
+// such a call has to return an error after its first enqueue, everything already in flight must
+// land first: otherwise the caller may free or reuse memory that a D2H copy is still writing.
+struct PipeGuard {
+  voda_ctx* c;
+  bool armed = true;
+  explicit PipeGuard(voda_ctx* ctx) : c(ctx) {}
+  ~PipeGuard() {
+    if (!armed) return;
+    cudaStreamSynchronize(c->pipe[0]);
+    cudaStreamSynchronize(c->pipe[1]);
+  }
+};
+
 // which arrays a policy reads (DESIGN.md "inputs per policy")
 enum : unsigned {
   F_SUBMIT = 1, F_FIRST = 2, F_PRIO = 4, F_NUM = 8, F_MIN = 16, F_MAX = 32, F_REM = 64, F_SPEED = 128
@@ -95,6 +112,34 @@ unsigned algo_fields(int algo) {
     case VODA_ALGO_AFSL: return F_SUBMIT | F_MIN | F_MAX | F_REM | F_SPEED;
   }
   return 0;
+}
+
+int max_i32(const int32_t* v, int a, int b) {
+  int m0 = INT32_MIN, m1 = INT32_MIN, m2 = INT32_MIN, m3 = INT32_MIN;
+  int i = a;
+  for (; i + 4 <= b; i += 4) {
+    m0 = std::max(m0, v[i]);
+    m1 = std::max(m1, v[i + 1]);
+    m2 = std::max(m2, v[i + 2]);
+    m3 = std::max(m3, v[i + 3]);
+  }
+  for (; i < b; i++) m0 = std::max(m0, v[i]);
+  return std::max(std::max(m0, m1), std::max(m2, m3));
+}
+
+// Largest speedup-table index jobs [j0, j1) can make their policy read (inclusive), from the
+// reference loops: FfDL g <= MaxNumProc (ffdl_optimizer.go:93-97); AFS-L S[r], S[r+1] with
+// r <= MaxNumProc and len(jb, r_champion) with r_champion < the largest MaxNumProc
+// (afsl.go:94-106), one more for the update that removes a job; ElasticTiresias S[min], S[min+1],
+// S[NumProc+1], S[r+1] with r <= max(MaxNumProc, MinNumProc) (elastic_tiresias.go:58,80,96,139,147).
+int speedup_index_cap(const voda_alloc_batch* b, int j0, int j1) {
+  long cap = max_i32(b->max_proc, j0, j1);
+  if (b->algo == VODA_ALGO_ELASTIC_TIRESIAS) {
+    cap = std::max<long>(cap, max_i32(b->min_proc, j0, j1));
+    cap = std::max<long>(cap, max_i32(b->num_proc, j0, j1));
+  }
+  cap = std::max<long>(cap, 1) + 2;
+  return (int)std::min<long>(cap, INT32_MAX - 1);
 }
 
 int check_batch(voda_ctx* ctx, const voda_alloc_batch* b) {
@@ -142,13 +187,42 @@ AllocArgs make_args(const voda_alloc_batch* b) {
   return a;
 }
 
+// Shapes the kernels cannot take (a function of algo, max_jobs, max_total, stride only), checked
+// before anything is enqueued.
+int check_shape(voda_ctx* ctx, const AllocArgs& a) {
+  switch (a.algo) {
+    case VODA_ALGO_FFDL_OPTIMIZER:
+      if (ffdl_smem_bytes(a) > 200 * 1024)
+        return fail(ctx, VODA_E_UNSUPPORTED, "FfDL: total_gpu / jobs too large for one CTA's shared memory");
+      return VODA_OK;
+    case VODA_ALGO_FIFO:
+    case VODA_ALGO_SRJF:
+    case VODA_ALGO_ELASTIC_FIFO:
+    case VODA_ALGO_ELASTIC_SRJF:
+      if (fill_smem_bytes(a) > 200 * 1024)
+        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
+      return VODA_OK;
+    case VODA_ALGO_TIRESIAS:
+    case VODA_ALGO_ELASTIC_TIRESIAS:
+      if (tiresias_smem_bytes(a, nullptr) > 220 * 1024)
+        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
+      return VODA_OK;
+    case VODA_ALGO_AFSL:
+      if (afsl_smem_bytes(a) > 220 * 1024)
+        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
+      return VODA_OK;
+    default:
+      return fail(ctx, VODA_E_UNSUPPORTED, "policy kernel not built into this library");
+  }
+}
+
 // Enqueue the kernels of one policy over `a` on `stream`.
 int dispatch_alloc(voda_ctx* ctx, const AllocArgs& a, DevBuf& scratch, cudaStream_t stream) {
   if (a.rounds == 0) return VODA_OK;
+  int shape = check_shape(ctx, a);
+  if (shape) return shape;
   switch (a.algo) {
     case VODA_ALGO_FFDL_OPTIMIZER: {
-      if (ffdl_smem_bytes(a) > 200 * 1024)
-        return fail(ctx, VODA_E_UNSUPPORTED, "FfDL: total_gpu / jobs too large for one CTA's shared memory");
       // every round keeps its slab of stored DP rows until the backtrack kernel has read it: cap the scratch
       // at 16 GiB and walk larger batches in sub-batches (two launches each)
       const size_t per = (ffdl_scratch_per_round(a) + 255) & ~(size_t)255;
@@ -167,23 +241,17 @@ int dispatch_alloc(voda_ctx* ctx, const AllocArgs& a, DevBuf& scratch, cudaStrea
     case VODA_ALGO_SRJF:
     case VODA_ALGO_ELASTIC_FIFO:
     case VODA_ALGO_ELASTIC_SRJF: {
-      if (fill_smem_bytes(a) > 200 * 1024)
-        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
       CU(launch_fill(a, ctx->sms, stream));
       ctx->launches += 1;
       return VODA_OK;
     }
     case VODA_ALGO_TIRESIAS:
     case VODA_ALGO_ELASTIC_TIRESIAS: {
-      if (tiresias_smem_bytes(a, nullptr) > 220 * 1024)
-        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
       CU(launch_tiresias(a, ctx->sms, stream));
       ctx->launches += 1;
       return VODA_OK;
     }
     case VODA_ALGO_AFSL: {
-      if (afsl_smem_bytes(a) > 220 * 1024)
-        return fail(ctx, VODA_E_UNSUPPORTED, "too many jobs per round for one CTA's shared memory");
       CU(launch_afsl(a, ctx->sms, stream));
       ctx->launches += 1;
       return VODA_OK;
@@ -226,6 +294,7 @@ int voda_ctx_create(int device, voda_ctx** out) {
   for (int i = 0; i < 2; i++)
     if ((e = cudaEventCreateWithFlags(&ctx->h2d_done[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if (const char* v = std::getenv("VODA_PACK_ROWS")) ctx->pack_rows = std::atoi(v) != 0;
+  if (const char* v = std::getenv("VODA_NARROW_COLS")) ctx->narrow_cols = std::atoi(v) != 0;
   *out = ctx;
   return VODA_OK;
 }
@@ -260,6 +329,11 @@ int voda_ctx_sync(voda_ctx* ctx) {
 }
 
 int64_t voda_ctx_launch_count(voda_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+void voda_ctx_copied_bytes(voda_ctx* ctx, int64_t* h2d, int64_t* d2h) {
+  if (h2d) *h2d = ctx ? ctx->h2d_bytes : 0;
+  if (d2h) *d2h = ctx ? ctx->d2h_bytes : 0;
+}
 
 const char* voda_last_error(voda_ctx* ctx) { return ctx ? ctx->err.c_str() : g_err_noctx.c_str(); }
 
@@ -348,6 +422,13 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
   }
   const unsigned f = algo_fields(b->algo);
   const size_t W = (f & F_SPEED) ? (size_t)b->speedup_stride : 0;
+  {  // refuse the shapes no kernel takes before anything is enqueued
+    AllocArgs probe = make_args(b);
+    probe.max_jobs = max_jobs;
+    probe.max_total = max_total;
+    rc = check_shape(ctx, probe);
+    if (rc) return rc;
+  }
   // bytes staged per job / per round
   size_t per_job = 4 /*out*/;
   if (f & F_SUBMIT) per_job += 8 + (b->submit_nsec ? 4 : 0);
@@ -366,6 +447,9 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
   size_t rounds_per_sz = std::max<size_t>((size_t)ctx->sms * 12, ((size_t)16 << 20) / bytes_per_round + 1);
   if (rounds_per_sz > (size_t)R) rounds_per_sz = (size_t)R;
   const int rounds_per = (int)rounds_per_sz;
+  ctx->h2d_bytes = 0;
+  ctx->d2h_bytes = 0;
+  PipeGuard guard(ctx);  // any error return below first waits for what is already in flight
   for (int c = 0, r0 = 0; r0 < R; c++, r0 += rounds_per) {
     const int r1 = std::min(R, r0 + rounds_per);
     const int slot = c & 1;
@@ -397,7 +481,8 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     // many bytes from host DRAM as the DMA engine would have moved, more slowly: measured
     // 10.1 ms vs 8.4 ms per 10k rounds on the 16-core box, so it is off by default
     const bool packed = ctx->pack_rows && b->algo == VODA_ALGO_FFDL_OPTIMIZER && W >= 8 && nj > 0;
-    size_t o_spoff = 0, packed_floats = 0;
+    size_t o_spoff = 0, packed_floats = 0, Wc = W;
+    bool narrow = false;
     if (packed) {
       if (!ctx->pool) {
         int t = (int)std::thread::hardware_concurrency() / 2;
@@ -424,15 +509,40 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
       o_sp = carve(4 * packed_floats);
       copies.push_back({o_sp, h_sp, 4 * packed_floats});
     } else if (f & F_SPEED) {
-      o_sp = in(b->speedup, 4 * W, j0, nj);
+      // Only the leading columns of the speedup table that the policy can index in this chunk
+      // cross PCIe: index g never exceeds a bound set by the chunk's largest MaxNumProc (and, for
+      // ElasticTiresias, MinNumProc / NumProc), so the device copy is a table of Wc <= W columns
+      // (2-D DMA: row width 4*Wc out of a host pitch of 4*W).  A kernel reading g >= Wc would see
+      // the Go map miss (0) — which is what the full table yields there only if g >= W, so Wc is
+      // used only when the bound proves no such read happens.
+      Wc = W;
+      if (ctx->narrow_cols && nj > 0) {
+        const size_t cap = (size_t)speedup_index_cap(b, j0, j1) + 1;
+        if (cap * 4 <= W * 3) Wc = cap;  // not worth a strided DMA for less than a quarter saved
+      }
+      if (Wc == W) {
+        o_sp = in(b->speedup, 4 * W, j0, nj);
+      } else {
+        o_sp = carve(4 * Wc * nj);
+        narrow = true;
+      }
     }
     const size_t o_og = carve(4 * nj), o_os = carve(4 * nr);
     rc = ensure(ctx, ctx->stage[slot], pos, s);
     if (rc) return rc;
     char* base = (char*)ctx->stage[slot].p;
-    for (const Copy& cp : copies) CU(cudaMemcpyAsync(base + cp.at, cp.src, cp.bytes, cudaMemcpyHostToDevice, s));
+    for (const Copy& cp : copies) {
+      CU(cudaMemcpyAsync(base + cp.at, cp.src, cp.bytes, cudaMemcpyHostToDevice, s));
+      ctx->h2d_bytes += (int64_t)cp.bytes;
+    }
+    if (narrow) {
+      CU(cudaMemcpy2DAsync(base + o_sp, 4 * Wc, b->speedup + (size_t)j0 * W, 4 * W, 4 * Wc, nj,
+                           cudaMemcpyHostToDevice, s));
+      ctx->h2d_bytes += (int64_t)(4 * Wc * nj);
+    }
     if (packed) CU(cudaEventRecord(ctx->h2d_done[slot], s));
     AllocArgs a = make_args(b);
+    if (narrow) a.stride = (int32_t)Wc;
     a.rounds = (int)nr;
     a.job_base = j0;
     a.max_jobs = max_jobs;
@@ -456,9 +566,11 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     if (rc) return rc;
     if (nj) CU(cudaMemcpyAsync(out_gpus + j0, base + o_og, 4 * nj, cudaMemcpyDeviceToHost, s));
     CU(cudaMemcpyAsync(out_status + r0, base + o_os, 4 * nr, cudaMemcpyDeviceToHost, s));
+    ctx->d2h_bytes += (int64_t)(4 * nj + 4 * nr);
   }
   CU(cudaStreamSynchronize(ctx->pipe[0]));
   CU(cudaStreamSynchronize(ctx->pipe[1]));
+  guard.armed = false;
   return VODA_OK;
 }
 
@@ -494,6 +606,9 @@ int voda_munkres_max(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t* A, 
   }
   CU(cudaSetDevice(ctx->device));
   const size_t per = (size_t)n * n * 8;
+  ctx->h2d_bytes = (int64_t)(per * (size_t)batch);
+  ctx->d2h_bytes = (int64_t)(4 * (size_t)batch * ((size_t)n + 1));
+  PipeGuard guard(ctx);
   // chunks big enough to occupy every SM (32 one-warp CTAs per SM), at least ~8 MiB
   size_t per_chunk = std::max<size_t>((size_t)ctx->sms * 32, (8u << 20) / per + 1);
   if (per_chunk > (size_t)batch) per_chunk = (size_t)batch;
@@ -516,6 +631,7 @@ int voda_munkres_max(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t* A, 
   }
   CU(cudaStreamSynchronize(ctx->pipe[0]));
   CU(cudaStreamSynchronize(ctx->pipe[1]));
+  guard.armed = false;
   return VODA_OK;
 }
 

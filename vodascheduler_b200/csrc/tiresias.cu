@@ -141,6 +141,7 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
       sm.misc[0] = 0;  // jobs inside a queue
       sm.misc[1] = 0;  // accepted in phase 3
       sm.misc[2] = 0;  // live jobs
+      sm.misc[3] = 0;  // greedy loop cut: the reference would never leave it
     }
     const bool packedKeys = __syncthreads_and(fits) != 0;
     auto S = [&](int i, int g) -> float {  // Info.Speedup[fmt.Sprint(g)], map miss => 0
@@ -307,6 +308,17 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
         __syncwarp();  // every lane has read the winner's state before its owner rewrites it
         if (rj == 0) {
           if (free >= (long long)mnj) {
+            if (mnj == 0) {
+              // MinNumProc == 0: the pick leaves r, free and the live list as they were and sets
+              // gain = S[1]-S[0] (:136-143).  If that is the gain the job already had, the next
+              // iteration sees the identical state and picks it again: the reference never
+              // returns.  Cut here (uniform across the warp: same shared values, same load).
+              const float ng = S(j, 1) - S(j, 0);
+              if (__float_as_int(ng) == __float_as_int(w.gain) && !(ng <= 0.0f)) {
+                if (lane == 0) sm.misc[3] = 1;
+                break;
+              }
+            }
             free -= mnj;
             if (owner) {
               sm.r[j] = mnj;
@@ -337,6 +349,10 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
     __syncthreads();
     for (int i = tid; i < n; i += nth) a.out_gpus[o + i] = sm.r[i];
     __syncthreads();
+    if (sm.misc[3]) {  // validateResult (:157) is never reached
+      if (tid == 0) a.out_status[rd] = VODA_ST_NONTERMINATING;
+      continue;
+    }
     const int v = block_validate(a, o, n, total, a.out_gpus + o, nullptr, sm.red);
     if (tid == 0) a.out_status[rd] = v;
   }

@@ -129,6 +129,28 @@ def quirk_batch(algo, rounds, jobs_per_round, total_gpu, seed=SEED + 1):
     return b
 
 
+def min_zero_batch(algo, rounds, jobs_per_round, total_gpu, seed=SEED + 2, frac=0.08):
+    """D.1 rounds in which a fraction of the jobs has MinNumProc == 0 — the input for which the
+    reference's ElasticTiresias greedy loop never ends (elastic_tiresias.go:136-143; reported as
+    VODA_ST_NONTERMINATING).  Those jobs get S[0] = S[1]/4 so that their first gain S[0]/0 is +Inf
+    rather than NaN (NaN sort keys are outside the reference's own domain)."""
+    b = jobs_batch(algo, rounds, jobs_per_round, total_gpu, seed, ragged=True, force_min1=False)
+    n = b.jobs
+    cnt = np.diff(b.job_off)
+    rnd = np.repeat(np.arange(rounds, dtype=np.int64), cnt)
+    job = np.arange(n, dtype=np.int64) - np.repeat(b.job_off[:-1].astype(np.int64), cnt)
+    z = _u(seed, rnd, job, 11) < frac
+    b.min_proc = np.where(z, 0, b.min_proc).astype(np.int32)
+    # half of them ask for more than any total: never started by the basic portion, they meet the
+    # greedy loop at 0 workers
+    big = z & (_u(seed, rnd, job, 12) < 0.5)
+    b.num_proc = np.where(big, 1 << 20, b.num_proc).astype(np.int32)
+    S = b.speedup.reshape(n, W).copy()
+    S[z, 0] = S[z, 1] * np.float32(0.25)
+    b.speedup = np.ascontiguousarray(S.reshape(-1))
+    return b
+
+
 def matrices(batch, n, kind="placement", seed=SEED, hi=8):
     """Appendix D.2 score matrices, int64 [batch, n, n].
 
