@@ -30,6 +30,7 @@
 // periodic compaction of the live list).
 #include "common.cuh"
 #include "kernels.h"
+#include "afsl_warp.cuh"
 
 namespace voda {
 namespace {
@@ -303,13 +304,58 @@ int afsl_hot_columns(const AllocArgs& a, int Jp) {
 
 }  // namespace
 
+// Rounds of up to 1024 jobs run with one warp per round (afsl_warp.cuh); larger rounds with the
+// four-warp kernel above.
+static int afsl_warp_columns(const AllocArgs& a, int Jp) {
+  // columns of 16-bit ranks (column 0 = rem, w = len(., w)): as many as keep the CTA at about
+  // 31 bytes of shared memory per job slot (seven 1024-job rounds per SM), more for small rounds
+  // (the SM holds at most 32 CTAs anyway), never more than the table is wide
+  long target = 31L * Jp;
+  if (target < 7000) target = 7000;
+  long nc = (target - (long)Jp * 10 - 32) / (2L * (Jp + 32));
+  if (nc < 1) nc = 1;
+  if (nc > a.stride) nc = a.stride;
+  if (nc < 1) nc = 1;
+  return (int)nc;
+}
+
 size_t afsl_smem_bytes(const AllocArgs& a) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
+  if (Jp <= 1024) {
+    const int Jw = Jp < 32 ? 32 : Jp;
+    return afslw::smem_bytes(Jw, afsl_warp_columns(a, Jw));
+  }
   return afsl_fixed_smem(Jp) + (size_t)afsl_hot_columns(a, Jp) * 4 * (size_t)Jp;
+}
+
+template <int SLOTS>
+static cudaError_t launch_afsl_warp(const AllocArgs& a, int sms, cudaStream_t stream) {
+  const int Jp = 32 * SLOTS;
+  const int NC = afsl_warp_columns(a, Jp);
+  const size_t smem = afslw::smem_bytes(Jp, NC);
+  auto kern = afslw::afsl_warp_kernel<SLOTS>;
+  if (smem > 48 * 1024) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+  }
+  int perSm = 0;
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, 32, smem);
+  if (e != cudaSuccess) return e;
+  if (perSm < 1) perSm = 1;
+  int grid = sms * perSm;
+  if (a.rounds < grid) grid = a.rounds;
+  kern<<<grid, 32, smem, stream>>>(a, NC);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
+  if (Jp <= 32) return launch_afsl_warp<1>(a, sms, stream);
+  if (Jp == 64) return launch_afsl_warp<2>(a, sms, stream);
+  if (Jp == 128) return launch_afsl_warp<4>(a, sms, stream);
+  if (Jp == 256) return launch_afsl_warp<8>(a, sms, stream);
+  if (Jp == 512) return launch_afsl_warp<16>(a, sms, stream);
+  if (Jp == 1024) return launch_afsl_warp<32>(a, sms, stream);
   const int CH = afsl_hot_columns(a, Jp);
   const size_t smem = afsl_fixed_smem(Jp) + (size_t)CH * 4 * (size_t)Jp;
   if (smem > 48 * 1024) {
