@@ -235,3 +235,86 @@ def test_ffdl_packed_rows_opt_in(oracle, monkeypatch):
             assert np.array_equal(s, s_ref) and np.array_equal(g, g_ref)
     finally:
         c.close()
+
+
+def _tie_heavy(b, seed=7):
+    """10 % of the jobs repeat their predecessor's SubmitTime / FirstStartTime / remaining time and a
+    fifth of the curves are flat from some count on: the stable-sort fall-backs (input order) and the
+    equal-gain / equal-length rules decide most picks."""
+    rng = np.random.default_rng(seed)
+    n = b.jobs
+    dup = np.nonzero(rng.random(n) < 0.10)[0]
+    dup = dup[dup > 0]
+    for name in ("submit_sec", "first_sec", "first_nsec", "remaining_sec"):
+        v = getattr(b, name).copy()
+        v[dup] = v[dup - 1]
+        setattr(b, name, v)
+    S = b.speedup.reshape(n, b.speedup_stride).copy()
+    flat = np.nonzero(rng.random(n) < 0.20)[0]
+    cap = rng.integers(1, 6, size=flat.size)
+    for i, c in zip(flat, cap):
+        S[i, c:] = S[i, c]
+    b.speedup = np.ascontiguousarray(S.reshape(-1))
+    return b
+
+
+@pytest.mark.parametrize("ties", [False, True], ids=["plain", "tie-heavy"])
+def test_ffdl_c2_shape_vs_structure_faithful_oracle(ctx, oracle, ties):
+    """BASELINE configs[1] shape (256 jobs x 1024 GPUs) against the STRUCTURE-FAITHFUL restatement
+    (string-keyed maps, the reference's own loop nest), not the dense one that shares the kernels'
+    derived forms."""
+    b = synth.jobs_batch("FfDLOptimizer", rounds=64, jobs_per_round=256, total_gpu=1024)
+    if ties:
+        b = _tie_heavy(b)
+    _same(ctx, oracle, b, dense=False, threads=8)
+
+
+@pytest.mark.parametrize("ties", [False, True], ids=["plain", "tie-heavy"])
+def test_afsl_c3_shape_vs_structure_faithful_oracle(ctx, oracle, ties):
+    """BASELINE configs[2] shape (1024 jobs x 4096 GPUs) against the structure-faithful restatement:
+    the literal left fold of afsl.go:72-92 with a map lookup per step — the check that the rank
+    columns, the first-beat passes and the champion cache of the kernel hold at full size, with heavy
+    ties."""
+    b = synth.jobs_batch("AFS-L", rounds=64, jobs_per_round=1024, total_gpu=4096)
+    if ties:
+        b = _tie_heavy(b)
+    g, s = _same(ctx, oracle, b, dense=False, threads=8)
+    assert (s == 0).all()
+
+
+@pytest.mark.parametrize("ties", [False, True], ids=["plain", "tie-heavy"])
+def test_tiresias_1024_jobs_vs_structure_faithful_oracle(ctx, oracle, ties):
+    """The stamp arg-max against the literal double stable sort per pick at 1024 jobs."""
+    b = synth.jobs_batch("ElasticTiresias", rounds=32, jobs_per_round=1024, total_gpu=4096)
+    if ties:
+        b = _tie_heavy(b)
+    _same(ctx, oracle, b, dense=False, threads=8)
+
+
+def test_afsl_more_than_1024_jobs(ctx, oracle):
+    """Rounds above 1024 jobs take the four-warp kernel; 1024 and below the one-warp kernel."""
+    for jobs, total in ((1500, 3000), (1025, 700)):
+        b = synth.jobs_batch("AFS-L", rounds=6, jobs_per_round=jobs, total_gpu=total)
+        _same(ctx, oracle, b)
+
+
+@pytest.mark.parametrize("jobs", [1, 31, 32, 33, 64, 100, 128, 200, 256, 500, 512, 513, 1000, 1024])
+def test_afsl_slot_widths(ctx, oracle, jobs):
+    """Every register-slot width of the one-warp kernel (1 .. 32 slots per lane), ragged rounds, a
+    budget that removes most jobs (compaction of the live list) and one that removes none."""
+    for total in (3 * jobs, max(1, jobs // 3)):
+        b = synth.jobs_batch("AFS-L", rounds=12, jobs_per_round=jobs, total_gpu=total, ragged=True)
+        _same(ctx, oracle, b)
+    q = synth.quirk_batch("AFS-L", rounds=40, jobs_per_round=jobs, total_gpu=2 * jobs)
+    _same(ctx, oracle, q)
+
+
+def test_afsl_large_worker_counts(ctx, oracle):
+    """Champions holding more workers than the rank table has columns (on-the-fly division), beyond
+    the table width (map miss: rem / 0) included."""
+    b = synth.jobs_batch("AFS-L", rounds=16, jobs_per_round=96, total_gpu=2500)
+    b.max_proc = (b.max_proc.astype(np.int64) * 3).astype(np.int32)
+    _same(ctx, oracle, b)
+    b = synth.jobs_batch("AFS-L", rounds=8, jobs_per_round=700, total_gpu=9000)
+    b.max_proc = np.where(np.arange(b.jobs) % 7 == 0, 60, b.max_proc).astype(np.int32)
+    _same(ctx, oracle, b)

@@ -83,8 +83,8 @@ __device__ __forceinline__ void row_rank(unsigned& bits, int rankA, int rankB, f
       "setp.ge.s32 ge, %1, %2;\n\t"
       "setp.leu.and.f32 t1, %3, %4, ge;\n\t"
       "setp.gt.and.f32 t2, %5, %6, !ge;\n\t"
-      "or.pred t1, t1, t2;\n\t"
-      "@t1 or.b32 %0, %0, %7;\n\t}"
+      "@t1 or.b32 %0, %0, %7;\n\t"
+      "@t2 or.b32 %0, %0, %7;\n\t}"
       : "+r"(bits)
       : "r"(rankA), "r"(rankB), "f"(Lc), "f"(Rb), "f"(Lb), "f"(Rc), "r"(bit));
 }
@@ -99,8 +99,8 @@ __device__ __forceinline__ void row_zero(unsigned& bits, int rankA, int rankB, u
       "setp.ne.b32 z, m, 0;\n\t"
       "setp.ge.and.s32 t1, %1, %2, z;\n\t"
       "setp.leu.and.f32 t2, %4, %5, !z;\n\t"
-      "or.pred t1, t1, t2;\n\t"
-      "@t1 or.b32 %0, %0, %6;\n\t}"
+      "@t1 or.b32 %0, %0, %6;\n\t"
+      "@t2 or.b32 %0, %0, %6;\n\t}"
       : "+r"(bits)
       : "r"(rankA), "r"(rankB), "r"(zeroBits), "f"(Lc), "f"(Rb), "r"(bit));
 }
@@ -164,9 +164,14 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
       continue;
     }
     __syncwarp();
-    auto S = [&](int job, int g) -> float {  // Info.Speedup[fmt.Sprint(g)], map miss => 0
-      if (g < 0 || g >= W) return 0.0f;
-      return a.speedup[(size_t)(o + job) * (size_t)W + (size_t)g];
+    // Info.Speedup[fmt.Sprint(g)], map miss => 0.  Offsets inside a round fit 32 bits (at most
+    // 1024 jobs x W entries): one IMAD per lookup instead of 64-bit address arithmetic.
+    const float* __restrict__ Sb = a.speedup + (size_t)o * (size_t)W;
+    const int32_t* __restrict__ mxb = a.max_proc + o;
+    const float* __restrict__ remb = a.remaining_sec + o;
+    auto S = [&](int job, int g) -> float {
+      if ((unsigned)g >= (unsigned)W) return 0.0f;
+      return Sb[(unsigned)(job * W + g)];
     };
     // ---- stable sort by SubmitTime (:42-44); ids are sorted positions from here on ---------
     {
@@ -217,8 +222,8 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
           L[k] = d / s1;
           Rr[k] = d / s0;
           aliveBits |= 1u << k;
-          remv[k] = a.remaining_sec[o + job];
-          maxmax = max(maxmax, a.max_proc[o + job]);
+          remv[k] = remb[job];
+          maxmax = max(maxmax, mxb[job]);
         } else {
           id[k] = Jp;
           L[k] = NEG_INF;
@@ -299,15 +304,15 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
       const int rc = sm.r[c];
       const int jobc = sm.perm[c];
       // what the update needs if this champion wins: in flight while the pass runs
-      const int mxc = a.max_proc[o + jobc];
+      const int mxc = mxb[jobc];
       const float sA = S(jobc, rc + 1), sB = S(jobc, rc + 2);
 
       // ---- one pass: every position >= pos against this champion -----------------------------------
       unsigned bits = 0;
       if (pos < len) {
         const int s0 = pos >> 5;
-        if (rc <= CH) {
-          const unsigned short* col = sm.rankT + (size_t)rc * pitch;
+        if (__builtin_expect(rc <= CH, 1)) {
+          const unsigned short* col = sm.rankT + rc * pitch;
           const int rk = col[c];
           const int rankA = rk == kNanRank ? -1 : rk;  // NaN: every '>=' is false
           if (rc == 0) {
@@ -334,12 +339,12 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
           }
         } else {
           // more workers than the table has columns: divide on the fly (w >= W is a map miss: rem / 0)
-          const float lenAf = a.remaining_sec[o + jobc] / S(jobc, rc);
+          const float lenAf = remb[jobc] / S(jobc, rc);
 #pragma unroll
           for (int k = 0; k < SLOTS; k++) {
             if (k >= s0 && k < sEnd && id[k] != Jp) {
               const int jb = sm.perm[id[k]];
-              const float lenB = a.remaining_sec[o + jb] / S(jb, rc);
+              const float lenB = remb[jb] / S(jb, rc);
               const bool b = (lenAf >= lenB) ? !(Lc > Rr[k]) : (L[k] > Rc);
               if (b) bits |= 1u << k;
             }
@@ -390,7 +395,7 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
       np = prevPos;
       pos = removed ? cp + 1 : cp;
       // ---- squeeze the dead slots out (uniform condition) ---------------------------------------
-      if (dead >= kCompactAt || (dead > 0 && dead * 4 >= len)) {
+      if (__builtin_expect(dead >= kCompactAt || (dead > 0 && dead * 4 >= len), 0)) {
         int base = 0;
 #pragma unroll
         for (int pass = 0; pass < 3; pass++) {

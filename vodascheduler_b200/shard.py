@@ -2,7 +2,7 @@
 data-path collective.  One process per GPU (torchrun); each rank takes a
 contiguous range of rounds, computes it on its own device through the C ABI, and the only
 exchange is an optional gather of the outputs plus a 4-number summary per rank
-(rounds, GPUs handed out, rounds that panicked, FNV-1a of the outputs) for a cross-rank check.
+(rounds, GPUs handed out, rounds that panicked, a digest of all the outputs) for a cross-rank check.
 
 `compute` is whatever maps a host AllocBatch to (gpus, status): Context.allocate on a GPU
 rank.  The host logic here is device-agnostic so it can be tested with the gloo backend.
@@ -19,18 +19,19 @@ def shard_bounds(rounds: int, world: int, rank: int):
     return rounds * rank // world, rounds * (rank + 1) // world
 
 
-def fnv1a(arr: np.ndarray) -> int:
-    h = np.uint64(0xCBF29CE484222325)
-    p = np.uint64(0x100000001B3)
-    with np.errstate(over="ignore"):
-        for b in np.ascontiguousarray(arr).view(np.uint8)[:1 << 20]:  # bounded: a checksum, not a proof
-            h = (h ^ np.uint64(b)) * p
-    return int(h)
+def digest64(arr: np.ndarray) -> int:
+    """63-bit digest of the WHOLE array (BLAKE2b, 8-byte digest): equal outputs <=> equal digests
+    for any practical purpose, at memory speed."""
+    import hashlib
+    h = hashlib.blake2b(np.ascontiguousarray(arr).view(np.uint8).data, digest_size=8).digest()
+    return int.from_bytes(h, "little") & 0x7FFFFFFFFFFFFFFF
 
 
 def summary(gpus: np.ndarray, status: np.ndarray) -> np.ndarray:
+    """Per-rank summary: rounds, GPUs handed out, rounds with a non-zero status, digest of all the
+    per-job outputs."""
     ok = status == 0
-    return np.array([status.size, int(gpus.sum()), int((~ok).sum()), fnv1a(gpus) & 0x7FFFFFFFFFFFFFFF], np.int64)
+    return np.array([status.size, int(gpus.astype(np.int64).sum()), int((~ok).sum()), digest64(gpus)], np.int64)
 
 
 def run_sharded(batch: AllocBatch, compute, rank: int, world: int, dist=None, gather: bool = True):

@@ -206,3 +206,97 @@ def place_batch(rounds, nodes, slots, jobs_per_round, seed=SEED, load=0.85):
             prev_off.append(len(prev_job))
     return PlaceBatch(node_off, node_slots, np.array(req_off), np.array(req_workers or [0])[:req_off[-1]],
                       np.array(prev_off), np.array(prev_job, dtype=np.int64), np.array(prev_workers, dtype=np.int64))
+
+
+# ---- generators that run on the device (plumbing: torch integer ops), so that the large
+#      throughput batches never cross PCIe.  Same counter-based PRNG, same values as the numpy
+#      generators above.
+def _i64(c):
+    return c - (1 << 64) if c >= (1 << 63) else c
+
+
+def _lsr(x, k):
+    return (x >> k) & ((1 << (64 - k)) - 1)
+
+
+def _splitmix64_t(x):
+    x = x + _i64(0x9E3779B97F4A7C15)
+    z = x
+    z = (z ^ _lsr(z, 30)) * _i64(0xBF58476D1CE4E5B9)
+    z = (z ^ _lsr(z, 27)) * _i64(0x94D049BB133111EB)
+    return z ^ _lsr(z, 31)
+
+
+def _u_t(seed, rnd, job, field):
+    """torch version of _u: int64 tensors in, float64 uniform [0,1) with 24 bits out."""
+    import torch
+    ctr = ((rnd << 20) | job) * 16 + field
+    base = _i64((seed * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF)
+    x = _splitmix64_t(ctr + base)
+    return _lsr(x, 40).to(torch.float64) / float(1 << 24)
+
+
+def matrices_device(batch, n, device, kind="placement", seed=SEED, hi=8, first=0, chunk=8192):
+    """matrices() generated on `device` (int64 [batch, n, n]); matrix b equals matrices()[first + b]."""
+    import torch
+    out = torch.empty((batch, n, n), dtype=torch.int64, device=device)
+    cells = torch.arange(n * n, dtype=torch.int64, device=device)[None, :]
+    for b0 in range(0, batch, chunk):
+        b1 = min(batch, b0 + chunk)
+        b = torch.arange(first + b0, first + b1, dtype=torch.int64, device=device)[:, None]
+        u = _u_t(seed + 7, b, cells, 0)
+        if kind == "uniform":
+            m = torch.floor(u * (hi + 1)).to(torch.int64)
+        else:
+            dense = torch.floor(_u_t(seed + 7, b, cells, 1) * (hi + 1)).to(torch.int64)
+            m = torch.where(u < 3.0 / max(3, n), torch.clamp(dense, min=1), torch.zeros_like(dense))
+        out[b0:b1] = m.view(b1 - b0, n, n)
+    return out
+
+
+def chain_batch(rounds, nodes, slots, jobs_per_round, seed=SEED, round_base=0, load=0.85):
+    """One scheduling round the way resched() runs it (scheduler.go:326-364): an Elastic-SRJF
+    allocation over `jobs_per_round` ready jobs with total = load * nodes * slots GPUs (a cluster
+    asked for every last slot sends bestFit into the loop the reference never leaves, Q12), whose result is the
+    request list of a placement round on `nodes` nodes x `slots` slots.  Returns (AllocBatch,
+    PlaceBatch); the PlaceBatch's req_workers is a placeholder to be replaced by the allocation
+    output (same offsets: req_off == job_off).  The previous layout packs a random earlier
+    allocation of the same jobs (1..8 workers, ~15 % of the jobs new) into the nodes in a random
+    job order, slot after slot, so jobs straddle node boundaries like a real history does."""
+    ab = jobs_batch("ElasticSRJF", rounds, jobs_per_round, int(load * nodes * slots), seed, round_base=round_base)
+    J = jobs_per_round
+    rnd = np.repeat(np.arange(rounds, dtype=np.int64) + round_base, J)
+    job = np.tile(np.arange(J, dtype=np.int64), rounds)
+    wprev = 1 + np.floor(_u(seed + 3, rnd, job, 0) * 8).astype(np.int64)
+    wprev[_u(seed + 3, rnd, job, 1) < 0.15] = 0                       # not running before
+    order = np.argsort(_u(seed + 3, rnd, job, 2).reshape(rounds, J), axis=1, kind="stable")
+    w = np.take_along_axis(wprev.reshape(rounds, J), order, axis=1)
+    end = np.cumsum(w, axis=1)
+    start = end - w
+    cap = nodes * slots
+    w = np.where(end <= cap, w, 0)                                     # jobs that did not fit were not running
+    end = start + w
+    # a job occupying slots [start, end) touches nodes start//slots .. (end-1)//slots (at most
+    # ceil(8/slots)+1 of them); emit one (node, job, workers) entry per touched node
+    span = int(np.ceil(8 / slots)) + 1
+    n0 = start // slots
+    ent_node, ent_job, ent_w, ent_round = [], [], [], []
+    rr = np.repeat(np.arange(rounds, dtype=np.int64)[:, None], J, axis=1)
+    for t in range(span):
+        nd = n0 + t
+        lo = np.maximum(start, nd * slots)
+        hi_ = np.minimum(end, (nd + 1) * slots)
+        ww = hi_ - lo
+        m = (ww > 0) & (w > 0)
+        ent_node.append(nd[m]); ent_job.append(order[m]); ent_w.append(ww[m]); ent_round.append(rr[m])
+    ent_node = np.concatenate(ent_node); ent_job = np.concatenate(ent_job)
+    ent_w = np.concatenate(ent_w); ent_round = np.concatenate(ent_round)
+    gnode = ent_round * nodes + ent_node
+    o = np.argsort(gnode, kind="stable")
+    gnode, ent_job, ent_w = gnode[o], ent_job[o], ent_w[o]
+    prev_off = np.zeros(rounds * nodes + 1, np.int64)
+    np.cumsum(np.bincount(gnode, minlength=rounds * nodes), out=prev_off[1:])
+    pb = PlaceBatch(np.arange(rounds + 1, dtype=np.int64) * nodes, np.full(rounds * nodes, slots, np.int64),
+                    ab.job_off.astype(np.int64), np.zeros(max(1, ab.jobs), np.int64)[:ab.jobs], prev_off, ent_job, ent_w,
+                    max_nodes=nodes, max_requests=J)
+    return ab, pb
