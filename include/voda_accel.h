@@ -326,6 +326,63 @@ int voda_tick(voda_ctx* ctx, const voda_tick_batch* host_batch);
 int voda_compare_results(voda_ctx* ctx, int32_t jobs, const int32_t* old_gpu, const int32_t* new_gpu,
                          const int32_t* status, int32_t* action);
 
+/* ---- trace replay: many what-if replicas of the scheduler's round loop ------------------------
+ * BASELINE configs[4].  One replica = one synthetic trace driven through the reference's round:
+ * resched() (pkg/scheduler/scheduler/scheduler.go:326-364) = ElasticSRJF.Schedule over the ready
+ * jobs, then PlacementManager.Place of the result (releaseSlots, bestFit, bindNodes,
+ * updateJobStates, updatePodNodeName: pkg/placement/placement_manager.go:306-617), triggered by job
+ * arrivals and completions (scheduler.go:648,670,887,955) and rate-limited to one round per
+ * rate_limit_sec (scheduler.go:212,297-311: 30 s).  A replica is sequential in simulated time, so
+ * the parallelism is ACROSS replicas: at every tick the rounds of all replicas that need one go to
+ * the GPU as one allocation batch and one placement batch (voda_allocate, voda_compare_results,
+ * voda_place on this context); the bookkeeping between the kernels (releaseSlots, updateJobStates,
+ * updatePodNodeName) runs on the host, replicas spread over host threads.
+ *
+ * Where the reference iterates a Go map (random order) this library uses a defined order: nodes by
+ * physical index; the requests of a round = the replica's live jobs in arrival order, zero
+ * allocations included (JobScheduleResult holds every ready job); a node's jobs in the order
+ * bestFit created them; a job's nodeNumSlotsList by physical node index (so worker pod i of a job
+ * sits on the i-th slot of that order, and a scale-down releases the highest node first, :356-359).
+ *
+ * Model of the cluster between rounds: a job holding w GPUs progresses at S[w] work-seconds per
+ * second (float64: remaining -= dt * S[min(w, W-1)]); it completes at the first tick that finds
+ * remaining <= 0; an idle cluster jumps to the next arrival.
+ * A round whose bestFit would never return in the reference (VODA_ST_NONTERMINATING) keeps the
+ * previous bindings (only updateJobStates runs) and is counted in placements_skipped.
+ */
+typedef struct {
+  int32_t        replicas;
+  const int32_t* job_off;        /* [replicas+1] jobs of replica k are [job_off[k], job_off[k+1]) */
+  const double*  arrival_sec;    /* [jobs] ascending inside a replica */
+  const double*  work_sec;       /* [jobs] serial work, seconds at one GPU */
+  const int32_t* min_proc;       /* [jobs] */
+  const int32_t* max_proc;       /* [jobs] */
+  const float*   speedup;        /* [jobs * speedup_stride] */
+  int32_t        speedup_stride;
+  const int32_t* nodes;          /* [replicas] nodes of the replica's cluster (<= 128) */
+  const int32_t* slots;          /* [replicas] slots per node */
+  const double*  rate_limit_sec; /* [replicas] */
+  int64_t        max_ticks;      /* stop after this many ticks (<= 0: run to completion) */
+  int32_t        host_threads;   /* bookkeeping threads (<= 0: one per four replicas, at most 16) */
+} voda_replay_batch;
+
+/* per replica k */
+typedef struct {
+  int64_t* rounds;              /* allocation+placement rounds run */
+  int64_t* done;                /* jobs completed */
+  double*  sim_time_sec;        /* simulated clock at the end */
+  double*  jct_sum_sec;         /* sum of job completion times */
+  int64_t* migrated_workers;    /* worker pods whose node changed (deletedWorkers, :592-596) */
+  int64_t* migrated_launchers;  /* jobs all of whose workers moved (:606-609) */
+  int64_t* placements_skipped;  /* rounds with VODA_ST_NONTERMINATING placement */
+  int64_t* actions;             /* [replicas*4] halts, scale-ins, scale-outs, starts (compareResults) */
+  uint64_t* history;            /* FNV-1a over every round's (tick, allocations, binding, score, cross,
+                                   migrated workers, migrated launchers) */
+  int64_t* ticks;               /* [1] ticks of the whole run */
+} voda_replay_out;
+
+int voda_replay(voda_ctx* ctx, const voda_replay_batch* batch, const voda_replay_out* out);
+
 #ifdef __cplusplus
 }
 #endif

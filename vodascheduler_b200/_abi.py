@@ -60,6 +60,19 @@ class CurveBatchStruct(C.Structure):  # voda_curve_batch
                 ("epoch_time_sec", C.c_void_p)]
 
 
+class ReplayBatchStruct(C.Structure):  # voda_replay_batch
+    _fields_ = [("replicas", C.c_int32), ("job_off", C.c_void_p), ("arrival_sec", C.c_void_p), ("work_sec", C.c_void_p),
+                ("min_proc", C.c_void_p), ("max_proc", C.c_void_p), ("speedup", C.c_void_p),
+                ("speedup_stride", C.c_int32), ("nodes", C.c_void_p), ("slots", C.c_void_p),
+                ("rate_limit_sec", C.c_void_p), ("max_ticks", C.c_int64), ("host_threads", C.c_int32)]
+
+
+class ReplayOutStruct(C.Structure):  # voda_replay_out
+    _fields_ = [("rounds", C.c_void_p), ("done", C.c_void_p), ("sim_time_sec", C.c_void_p), ("jct_sum_sec", C.c_void_p),
+                ("migrated_workers", C.c_void_p), ("migrated_launchers", C.c_void_p), ("placements_skipped", C.c_void_p),
+                ("actions", C.c_void_p), ("history", C.c_void_p), ("ticks", C.c_void_p)]
+
+
 TICK_MAX_QUEUES = 8
 JOB_SUBMITTED, JOB_WAITING, JOB_RUNNING, JOB_COMPLETED, JOB_FAILED = range(5)
 ACT_NONE, ACT_HALT, ACT_SCALE_IN, ACT_SCALE_OUT, ACT_START = range(5)
@@ -101,6 +114,7 @@ PROTOTYPES = {
     "voda_tick_dev": (C.c_int, [C.c_void_p, C.POINTER(TickBatchStruct)]),
     "voda_compare_results": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "voda_compare_results_dev": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "voda_replay": (C.c_int, [C.c_void_p, C.POINTER(ReplayBatchStruct), C.POINTER(ReplayOutStruct)]),
     "voda_build_curves": (C.c_int, [C.c_void_p, C.POINTER(CurveBatchStruct), C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p]),
     "voda_build_curves_dev": (C.c_int, [C.c_void_p, C.POINTER(CurveBatchStruct), C.c_void_p, C.c_void_p, C.c_void_p,

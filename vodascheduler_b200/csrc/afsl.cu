@@ -28,6 +28,9 @@
 // so shared memory per round is kept small (32 bytes per job + CH * 4) to fit 4 CTAs per SM.
 // Jobs are relabelled by their sorted position; removal at max keeps order (lazy deletion +
 // periodic compaction of the live list).
+#include <algorithm>
+#include <cstdlib>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "afsl_warp.cuh"
@@ -314,6 +317,7 @@ static int afsl_warp_columns(const AllocArgs& a, int Jp) {
   if (target < 7000) target = 7000;
   long nc = (target - (long)Jp * 10 - 32) / (2L * (Jp + 32));
   if (nc < 1) nc = 1;
+  if (const char* v = std::getenv("VODA_AFSL_NC")) nc = std::atoi(v);
   if (nc > a.stride) nc = a.stride;
   if (nc < 1) nc = 1;
   return (int)nc;
@@ -342,6 +346,7 @@ static cudaError_t launch_afsl_warp(const AllocArgs& a, int sms, cudaStream_t st
   cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, 32, smem);
   if (e != cudaSuccess) return e;
   if (perSm < 1) perSm = 1;
+  if (const char* v = std::getenv("VODA_AFSL_CTAS")) perSm = std::max(1, std::min(perSm, std::atoi(v)));
   int grid = sms * perSm;
   if (a.rounds < grid) grid = a.rounds;
   kern<<<grid, 32, smem, stream>>>(a, NC);
@@ -350,12 +355,13 @@ static cudaError_t launch_afsl_warp(const AllocArgs& a, int sms, cudaStream_t st
 
 cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  if (Jp <= 32) return launch_afsl_warp<1>(a, sms, stream);
-  if (Jp == 64) return launch_afsl_warp<2>(a, sms, stream);
-  if (Jp == 128) return launch_afsl_warp<4>(a, sms, stream);
-  if (Jp == 256) return launch_afsl_warp<8>(a, sms, stream);
-  if (Jp == 512) return launch_afsl_warp<16>(a, sms, stream);
-  if (Jp == 1024) return launch_afsl_warp<32>(a, sms, stream);
+  const bool warp = true;
+  if (warp && Jp <= 32) return launch_afsl_warp<1>(a, sms, stream);
+  if (warp && Jp == 64) return launch_afsl_warp<2>(a, sms, stream);
+  if (warp && Jp == 128) return launch_afsl_warp<4>(a, sms, stream);
+  if (warp && Jp == 256) return launch_afsl_warp<8>(a, sms, stream);
+  if (warp && Jp == 512) return launch_afsl_warp<16>(a, sms, stream);
+  if (warp && Jp == 1024) return launch_afsl_warp<32>(a, sms, stream);
   const int CH = afsl_hot_columns(a, Jp);
   const size_t smem = afsl_fixed_smem(Jp) + (size_t)CH * 4 * (size_t)Jp;
   if (smem > 48 * 1024) {

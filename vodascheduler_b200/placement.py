@@ -194,7 +194,10 @@ class PlacementManager:
             logical[i].name = current[int(out.phys_of_logical[node_base + i])].name  # rename (:509-511)
         self.lastScore = int(out.score[rnd])
         self.lastCrossNode = int(out.cross[rnd])
-        self.nodeStates = {nd.name: nd for nd in logical}
+        # Go keeps nodeStates in a map (random iteration order); here the physical nodes keep their
+        # first order for ever, the defined order of include/voda_accel.h ("trace replay")
+        by_name = {nd.name: nd for nd in logical}
+        self.nodeStates = {cur.name: by_name[cur.name] for cur in current}
         self.updateJobStates()
         return self.updatePodNodeName()
 
