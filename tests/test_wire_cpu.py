@@ -43,7 +43,8 @@ def test_decode_request():
     assert (j.Config.NumProc, j.Config.MinNumProc, j.Config.MaxNumProc, j.Config.Epochs) == (2, 1, 4, 30)
     assert j.Metrics.FirstStartTime == Time(1635660000, 0)
     assert j.Info.EstimatedRemainningTimeSec == 321.5
-    assert j.Info.Speedup == {"0": 0.0, "1": 1.0, "2": 1.8, "4": 3.1}
+    f32 = lambda x: float(__import__("numpy").float32(x))  # map[string]float32: the values are float32
+    assert j.Info.Speedup == {"0": 0.0, "1": 1.0, "2": f32(1.8), "4": f32(3.1)}
 
 
 def test_decode_defaults_like_encoding_json():
@@ -72,3 +73,21 @@ def test_handler_rejects_without_touching_the_gpu():
     assert code == 400 and json.loads(body) == {"error": "Not found"}
     code, _ = wire.handle_allocation('{"AlgorithmName":"FIFO","ReadyJobs":[{"job_name":"a","submit_timestamp":"yesterday"}]}')
     assert code == 400
+
+
+def test_float_fields_round_once_to_float32():
+    """encoding/json parses a float32 field straight from the decimal text (ParseFloat(s, 32)).  A
+    decimal a hair above the midpoint of two float32 values rounds UP there; going through float64
+    first lands exactly on the midpoint and ties-to-even rounds it DOWN."""
+    import numpy as np
+    from vodascheduler_b200 import wire
+    above = "1.000000059604644775390625000000000000000000001"  # 1 + 2^-24 + epsilon
+    up = float(np.float32(1.0) + np.float32(2.0 ** -23))
+    assert float(np.float32(float(above))) == 1.0          # the double rounding this avoids
+    assert wire.parse_float32(above) == up
+    assert wire.parse_float32("1.000000059604644775390625") == 1.0   # the exact midpoint: ties to even
+    assert wire.parse_float32("0.1") == float(np.float32(0.1))
+    body = '{"SchedulerID":"s","NumGpu":1,"AlgorithmName":"ElasticSRJF","ReadyJobs":[{"job_name":"a",' \
+           '"info":{"estimate_remainning_time_seconds":%s,"speedup":{"1":%s}}}]}' % (above, above)
+    req = wire.AllocationRequest.from_json(body)
+    assert req.ReadyJobs[0].Info.EstimatedRemainningTimeSec == up and req.ReadyJobs[0].Info.Speedup["1"] == up

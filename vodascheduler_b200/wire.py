@@ -19,6 +19,8 @@ from __future__ import annotations
 
 import datetime as _dt
 import json
+
+import numpy as np
 import re
 from typing import Dict, List, Sequence, Tuple, Union
 
@@ -53,6 +55,27 @@ def format_time(t: Time) -> str:
     frac = f".{t.nsec:09d}".rstrip("0") if t.nsec else ""
     return (f"{base.year:04d}-{base.month:02d}-{base.day:02d}T{base.hour:02d}:{base.minute:02d}:{base.second:02d}"
             + frac + "Z")
+
+
+def parse_float32(text: str) -> float:
+    """A JSON number as Go's encoding/json stores it into a float32 field: the decimal text rounded
+    ONCE to the nearest float32 (strconv.ParseFloat(s, 32)).  Rounding to float64 first and to float32
+    afterwards differs when the float64 lands exactly half-way between two float32 values while the
+    decimal itself is a hair to one side; that case is resolved with exact rational arithmetic."""
+    x = float(text)
+    with np.errstate(over="ignore"):
+        f = np.float32(x)
+    if not np.isfinite(f) or float(f) == x:
+        return float(f)
+    lo, hi = np.float32(np.nextafter(x, -np.inf)), np.float32(np.nextafter(x, np.inf))
+    if lo != hi:  # x is a float32 midpoint: the side is decided by the exact decimal
+        from fractions import Fraction
+        exact, mid = Fraction(text), Fraction(x)
+        if exact > mid:
+            return float(hi)
+        if exact < mid:
+            return float(lo)
+    return float(f)
 
 
 def job_from_json(o: dict) -> TrainingJob:
@@ -98,7 +121,8 @@ class AllocationRequest:
 
     @staticmethod
     def from_json(body: Union[str, bytes, dict]) -> "AllocationRequest":
-        o = json.loads(body) if isinstance(body, (str, bytes, bytearray)) else body
+        # float fields of the request are float32 in Go (trainingjob.go:63-66): parse them as such
+        o = json.loads(body, parse_float=parse_float32) if isinstance(body, (str, bytes, bytearray)) else body
         return AllocationRequest(o.get("SchedulerID", ""), int(o.get("NumGpu", 0)), o.get("AlgorithmName", ""),
                                  [job_from_json(j) for j in (o.get("ReadyJobs") or [])])
 
