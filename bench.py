@@ -472,7 +472,7 @@ def run_chain(name, wl, ctx, env, steps, warmup, e2e_steps, with_cpu):
             "status": torch.full((R,), -1, dtype=torch.int32, device=env.dev)}
     po = _abi.PlaceOutStruct()
     for k, _ in _abi.PlaceOutStruct._fields_:
-        setattr(po, k, outs[k].data_ptr())
+        setattr(po, k, outs[k].data_ptr() if k in outs else None)
 
     def step_dev():
         ctx.allocate_dev(dab, d_g, d_s)

@@ -199,6 +199,13 @@ int voda_munkres_max_dev(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t*
  *   prev_workers                 over the flat node index: entries of node i are
  *                                [prev_off[i], prev_off[i+1]), prev_job is a round-local job
  *                                index, prev_workers its jobNumWorkers value on that node.
+ *   pods_off / pods_node /       OPTIONAL (all three or none): the pod -> node table the round starts
+ *   pods_slots                   from (pm.podNodeName, :571-617), run-length coded per request: the
+ *                                runs of request q (flat index req_off[r] + q) are [pods_off[q],
+ *                                pods_off[q+1]), run t puts the next pods_slots[t] worker pods of the job
+ *                                (pod index ascending) on physical node pods_node[t] — the job's
+ *                                nodeNumSlotsList as updateJobStates left it BEFORE this round's
+ *                                releaseSlots.  With it the kernel also counts the pods the round moves.
  */
 typedef struct {
   int32_t        rounds;
@@ -211,6 +218,9 @@ typedef struct {
   const int32_t* prev_workers;  /* [prev entries] */
   int32_t        max_nodes;     /* upper bound of nodes per round (<= 128); 0 -> computed    */
   int32_t        max_requests;  /* upper bound of requests per round;       0 -> computed    */
+  const int32_t* pods_off;      /* [requests+1] or NULL */
+  const int32_t* pods_node;     /* [pod runs] */
+  const int32_t* pods_slots;    /* [pod runs] */
 } voda_place_batch;
 
 /*
@@ -227,6 +237,13 @@ typedef struct {
  *   out_status[r]                         VODA_ST_OK / VODA_ST_NONTERMINATING / VODA_ST_BOUND;
  *                                         the other outputs of a round are unspecified
  *                                         unless its status is VODA_ST_OK
+ *   out_migrated_workers[r]               OPTIONAL, needs pods_*: worker pods whose node changes
+ *   out_migrated_launchers[r]             (deletedWorkers, :592-596) and jobs ALL of whose workers
+ *                                         move, so that their launcher is deleted too
+ *                                         (deletedLaunchers, :606-609) — updateJobStates +
+ *                                         updatePodNodeName (:548-617) on the new binding, with a
+ *                                         job's nodes taken by physical index (the reference takes
+ *                                         them in Go map order: any order is one it could produce)
  */
 typedef struct {
   int32_t* phys_of_logical;  /* [nodes] */
@@ -238,6 +255,8 @@ typedef struct {
   int64_t* score;            /* [R] */
   int32_t* cross;            /* [R] */
   int32_t* status;           /* [R] */
+  int32_t* migrated_workers;    /* [R] or NULL */
+  int32_t* migrated_launchers;  /* [R] or NULL */
 } voda_place_out;
 
 int voda_place(voda_ctx* ctx, const voda_place_batch* host_batch, const voda_place_out* host_out);

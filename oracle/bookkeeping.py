@@ -135,3 +135,21 @@ class Manager:
                 deleted_launchers += 1
         self.podNodeName = new_table
         return deleted_workers, deleted_launchers
+
+
+def pod_table(manager, names):
+    """pm.podNodeName as the run-length arrays voda_place takes (pods_off / pods_node / pods_slots):
+    for every job of `names`, in order, the node of its worker pods 0, 1, 2, ... run-length coded."""
+    off, node, slots = [0], [], []
+    for job in names:
+        idx = 0
+        while (job, idx) in manager.podNodeName:
+            nd = manager.podNodeName[(job, idx)]
+            if len(node) > off[-1] and node[-1] == nd:
+                slots[-1] += 1
+            else:
+                node.append(nd)
+                slots.append(1)
+            idx += 1
+        off.append(len(node))
+    return off, node, slots

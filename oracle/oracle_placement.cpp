@@ -100,6 +100,8 @@ int64_t score(const nodeState& position, const nodeState& candidate) {
 
 void run(const voda_place_batch* b, const voda_place_out* out, int32_t r0, int32_t r1) {
   for (int32_t r = r0; r < r1; r++) {
+    if (out->migrated_workers) out->migrated_workers[r] = 0;
+    if (out->migrated_launchers) out->migrated_launchers[r] = 0;
     const int32_t n0 = b->node_off[r], n = b->node_off[r + 1] - n0;
     const int32_t q0 = b->req_off[r], m = b->req_off[r + 1] - q0;
     const int32_t e0 = q0 + n0;
@@ -144,6 +146,36 @@ void run(const voda_place_batch* b, const voda_place_out* out, int32_t r0, int32
     out->score[r] = total;
     out->cross[r] = (int32_t)cross;
     out->status[r] = VODA_ST_OK;
+    if (b->pods_off && out->migrated_workers && out->migrated_launchers) {
+      // rename (:509-511), updateJobStates (:548-566) with the nodes taken by physical index,
+      // updatePodNodeName (:571-617) against the caller's pod table
+      std::vector<int32_t> logicalOf((size_t)n);
+      for (int32_t i = 0; i < n; i++) logicalOf[(size_t)colOfRow[(size_t)i]] = i;
+      int64_t deletedWorkers = 0, deletedLaunchers = 0;
+      for (int32_t q = 0; q < m; q++) {
+        const std::string name = "job-" + std::to_string(q);
+        std::vector<int32_t> newPods;  // node of worker pod idx
+        bool present = false;
+        for (int32_t c = 0; c < n; c++) {
+          const auto& jw = logical[(size_t)logicalOf[(size_t)c]].jobNumWorkers;
+          auto it = jw.find(name);
+          if (it == jw.end()) continue;
+          present = true;
+          for (long k = 0; k < it->second; k++) newPods.push_back(c);
+        }
+        if (!present) continue;
+        std::vector<int32_t> oldPods;
+        for (int32_t t = b->pods_off[q0 + q]; t < b->pods_off[q0 + q + 1]; t++)
+          for (int32_t k = 0; k < b->pods_slots[t]; k++) oldPods.push_back(b->pods_node[t]);
+        long deleted = 0;
+        for (size_t idx = 0; idx < newPods.size() && idx < oldPods.size(); idx++)
+          if (newPods[idx] != oldPods[idx]) deleted++;
+        deletedWorkers += deleted;
+        if (deleted == (long)newPods.size()) deletedLaunchers++;
+      }
+      out->migrated_workers[r] = (int32_t)deletedWorkers;
+      out->migrated_launchers[r] = (int32_t)deletedLaunchers;
+    }
   }
 }
 

@@ -119,3 +119,62 @@ def test_cpu_replay_runs_to_completion(oracle):
     b = orp.replay_one(r.trace, r.nodes, r.slots, r.rate_limit, dense=False)
     assert a == b                      # dense and structure-faithful allocation ports agree round for round
     assert a["done"] == 60 and a["rounds"] > 5 and a["actions"]["starts"] >= 60
+
+
+def _random_rounds(seed, nodes, slots, rounds):
+    """A random history of request maps that stays clear of the reference's endless loop."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    jobs, nxt = {}, 0
+    for _ in range(rounds):
+        for j in list(jobs):
+            u = rng.random()
+            if u < 0.15:
+                del jobs[j]
+            elif u < 0.5:
+                jobs[j] = int(rng.integers(0, 7))
+        for _ in range(int(rng.integers(0, 3))):
+            jobs[f"job{nxt}"] = int(rng.integers(1, 7))
+            nxt += 1
+        while sum(jobs.values()) > int(0.8 * nodes * slots):
+            jobs[max(jobs, key=jobs.get)] -= 1
+        yield dict(jobs)
+
+
+def place_round(place_fn, ref, req, nodes, slots):
+    """One Place() through `place_fn` (oracle.place or Context.place) with the pod table attached,
+    applied to the bookkeeping restatement `ref`; returns (counts from the placement call, counts from
+    updatePodNodeName of the restatement)."""
+    import numpy as np
+    from vodascheduler_b200.batch import PlaceBatch
+    names = list(req)
+    pods = bk.pod_table(ref, names)  # the table the round starts from
+    ref.release_slots(req)
+    index = {n: q for q, n in enumerate(names)}
+    off, pj, pw = [0], [], []
+    for ent in ref.previous_layout(index):
+        for q, w in ent:
+            pj.append(q)
+            pw.append(w)
+        off.append(len(pj))
+    out = place_fn(PlaceBatch([0, nodes], [slots] * nodes, [0, len(names)], [req[n] for n in names], off,
+                              np.array(pj, np.int64), np.array(pw, np.int64), pods_off=pods[0],
+                              pods_node=np.array(pods[1], np.int64), pods_slots=np.array(pods[2], np.int64)))
+    assert out.status[0] == 0
+    lay = [(int(out.lay_node[t]), names[int(out.lay_job[t])], int(out.lay_workers[t])) for t in range(int(out.lay_cnt[0]))]
+    ref.bind(lay, [int(x) for x in out.free_slots[:nodes]], [int(x) for x in out.phys_of_logical[:nodes]])
+    ref.update_job_states()
+    return (int(out.migrated_workers[0]), int(out.migrated_launchers[0])), ref.update_pod_node_name()
+
+
+def test_oracle_place_migration_counts_equal_bookkeeping(oracle):
+    """voda_oracle_place's migrated_workers / migrated_launchers (computed from the binding and the
+    run-length pod table) against updatePodNodeName of the bookkeeping restatement, round after round."""
+    nodes, slots = 6, 8
+    ref = bk.Manager(nodes, slots)
+    moved = 0
+    for req in _random_rounds(5, nodes, slots, 80):
+        got, want = place_round(oracle.place, ref, req, nodes, slots)
+        assert got == want
+        moved += want[0]
+    assert moved > 0

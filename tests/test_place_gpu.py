@@ -78,3 +78,51 @@ def test_ragged_batch(ctx, oracle):
         rounds.append(dict(nodes=nodes, requests=req, prev=prev))
     pb = place_batch_from(rounds)
     _same(pb, ctx.place(pb), oracle.place(pb))
+
+
+def _pods_from_prev(pb):
+    """A pod table consistent with the previous layout of a synthetic PlaceBatch: every job's worker
+    pods sit, in pod-index order, on the nodes that hold it (by physical index)."""
+    off, node, slots = [0], [], []
+    for r in range(pb.rounds):
+        n0, n1 = int(pb.node_off[r]), int(pb.node_off[r + 1])
+        per_job = {}
+        for c in range(n0, n1):
+            for e in range(int(pb.prev_off[c]), int(pb.prev_off[c + 1])):
+                per_job.setdefault(int(pb.prev_job[e]), []).append((c - n0, int(pb.prev_workers[e])))
+        for q in range(int(pb.req_off[r + 1]) - int(pb.req_off[r])):
+            for c, w in per_job.get(q, []):
+                node.append(c)
+                slots.append(w)
+            off.append(len(node))
+    return np.array(off, np.int32), np.array(node, np.int32), np.array(slots, np.int32)
+
+
+def test_migration_counts_match_oracle(ctx, oracle):
+    """migrated_workers / migrated_launchers of the kernel (updateJobStates + updatePodNodeName as
+    counts, placement_manager.go:548-617) against the CPU restatement, over batched rounds."""
+    pb = synth.place_batch(rounds=300, nodes=24, slots=8, jobs_per_round=40)
+    pb.pods_off, pb.pods_node, pb.pods_slots = _pods_from_prev(pb)
+    ref = oracle.place(pb, threads=4)
+    out = ctx.place(pb)
+    assert np.array_equal(out.status, ref.status)
+    ok = ref.status == 0
+    assert np.array_equal(out.migrated_workers[ok], ref.migrated_workers[ok])
+    assert np.array_equal(out.migrated_launchers[ok], ref.migrated_launchers[ok])
+    assert ref.migrated_workers[ok].sum() > 0 and ref.migrated_launchers[ok].sum() > 0
+    # without a pod table nothing is counted and nothing else changes
+    pb.pods_off = pb.pods_node = pb.pods_slots = None
+    plain = ctx.place(pb)
+    assert np.array_equal(plain.phys_of_logical, out.phys_of_logical) and not plain.migrated_workers.any()
+
+
+def test_migration_counts_match_bookkeeping_history(ctx):
+    """A history of rounds: the kernel's counts equal updatePodNodeName of the bookkeeping
+    restatement fed with the kernel's own bindings."""
+    from oracle import bookkeeping as bk
+    from test_bookkeeping_cpu import _random_rounds, place_round
+    nodes, slots = 6, 8
+    ref = bk.Manager(nodes, slots)
+    for req in _random_rounds(9, nodes, slots, 80):
+        got, want = place_round(ctx.place, ref, req, nodes, slots)
+        assert got == want

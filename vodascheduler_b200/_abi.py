@@ -43,6 +43,7 @@ class PlaceBatchStruct(C.Structure):
         ("req_off", C.c_void_p), ("req_workers", C.c_void_p),
         ("prev_off", C.c_void_p), ("prev_job", C.c_void_p), ("prev_workers", C.c_void_p),
         ("max_nodes", C.c_int32), ("max_requests", C.c_int32),
+        ("pods_off", C.c_void_p), ("pods_node", C.c_void_p), ("pods_slots", C.c_void_p),
     ]
 
 
@@ -51,6 +52,7 @@ class PlaceOutStruct(C.Structure):
         ("phys_of_logical", C.c_void_p), ("free_slots", C.c_void_p), ("lay_cnt", C.c_void_p),
         ("lay_node", C.c_void_p), ("lay_job", C.c_void_p), ("lay_workers", C.c_void_p),
         ("score", C.c_void_p), ("cross", C.c_void_p), ("status", C.c_void_p),
+        ("migrated_workers", C.c_void_p), ("migrated_launchers", C.c_void_p),
     ]
 
 

@@ -21,6 +21,8 @@ _ALLOC_ARRAYS = (
     ("remaining_sec", np.float32), ("speedup", np.float32),
 )
 
+_PLACE_OPTIONAL = (("pods_off", np.int32), ("pods_node", np.int32), ("pods_slots", np.int32))
+
 _PLACE_ARRAYS = (
     ("node_off", np.int32), ("node_slots", np.int32), ("req_off", np.int32),
     ("req_workers", np.int32), ("prev_off", np.int32), ("prev_job", np.int32),
@@ -129,9 +131,9 @@ class PlaceBatch:
     """R placement rounds (see voda_place_batch in include/voda_accel.h)."""
 
     def __init__(self, node_off, node_slots, req_off, req_workers, prev_off, prev_job,
-                 prev_workers, max_nodes=0, max_requests=0):
+                 prev_workers, max_nodes=0, max_requests=0, pods_off=None, pods_node=None, pods_slots=None):
         loc = locals()
-        for name, dt in _PLACE_ARRAYS:
+        for name, dt in _PLACE_ARRAYS + _PLACE_OPTIONAL:
             v = loc[name]
             if isinstance(v, (np.ndarray, list, tuple)):
                 v = np.ascontiguousarray(np.asarray(v, dtype=dt).reshape(-1))
@@ -154,8 +156,8 @@ class PlaceBatch:
     def struct(self):
         s = _abi.PlaceBatchStruct()
         s.rounds = self.rounds
-        for name, _ in _PLACE_ARRAYS:
-            setattr(s, name, _ptr(getattr(self, name)))
+        for name, _ in _PLACE_ARRAYS + _PLACE_OPTIONAL:
+            setattr(s, name, _ptr(getattr(self, name, None)))
         s.max_nodes, s.max_requests = self.max_nodes, self.max_requests
         return s
 
@@ -168,6 +170,9 @@ class PlaceBatch:
         b.max_requests = self.max_requests or int(np.diff(self.req_off).max(initial=0))
         for name, _ in _PLACE_ARRAYS:
             setattr(b, name, torch.from_numpy(getattr(self, name)).to(device))
+        for name, _ in _PLACE_OPTIONAL:
+            v = getattr(self, name, None)
+            setattr(b, name, None if v is None else torch.from_numpy(v).to(device))
         return b
 
 
@@ -185,6 +190,8 @@ class PlaceOut:
         self.score = np.zeros(max(1, rounds), np.int64)
         self.cross = np.zeros(max(1, rounds), np.int32)
         self.status = np.full(max(1, rounds), -1, np.int32)
+        self.migrated_workers = np.zeros(max(1, rounds), np.int32)
+        self.migrated_launchers = np.zeros(max(1, rounds), np.int32)
 
     def struct(self):
         s = _abi.PlaceOutStruct()

@@ -650,6 +650,11 @@ static PlaceArgs make_place_args(const voda_place_batch* b, const voda_place_out
   a.node_off = b->node_off; a.node_slots = b->node_slots; a.req_off = b->req_off; a.req_workers = b->req_workers;
   a.prev_off = b->prev_off; a.prev_job = b->prev_job; a.prev_workers = b->prev_workers;
   a.max_nodes = b->max_nodes; a.max_requests = b->max_requests;
+  const bool pods = b->pods_off && o->migrated_workers && o->migrated_launchers;
+  a.pods_off = pods ? b->pods_off : nullptr; a.pods_node = pods ? b->pods_node : nullptr;
+  a.pods_slots = pods ? b->pods_slots : nullptr;
+  a.migrated_workers = pods ? o->migrated_workers : nullptr;
+  a.migrated_launchers = pods ? o->migrated_launchers : nullptr;
   a.phys_of_logical = o->phys_of_logical; a.free_slots = o->free_slots; a.lay_cnt = o->lay_cnt;
   a.lay_node = o->lay_node; a.lay_job = o->lay_job; a.lay_workers = o->lay_workers;
   a.score = reinterpret_cast<long long*>(o->score); a.cross = o->cross; a.status = o->status;
@@ -704,6 +709,11 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   const size_t i_no = carve(4 * (size_t)(R + 1)), i_ns = carve(4 * (size_t)nodes), i_ro = carve(4 * (size_t)(R + 1)),
                i_rw = carve(4 * (size_t)reqs), i_po = carve(4 * (size_t)(nodes + 1)), i_pj = carve(4 * (size_t)prevs),
                i_pw = carve(4 * (size_t)prevs);
+  const bool pods = b->pods_off && o->migrated_workers && o->migrated_launchers;
+  const int podRuns = pods ? b->pods_off[reqs] : 0;
+  if (pods && podRuns > 0 && (!b->pods_node || !b->pods_slots)) return fail(ctx, VODA_E_INVALID, "pods_node / pods_slots missing");
+  const size_t i_qo = carve(pods ? 4 * (size_t)(reqs + 1) : 0), i_qn = carve(4 * (size_t)podRuns), i_qs = carve(4 * (size_t)podRuns);
+  const size_t o_mw = carve(pods ? 4 * (size_t)R : 0), o_ml = carve(pods ? 4 * (size_t)R : 0);
   const size_t o_ph = carve(4 * (size_t)nodes), o_fr = carve(4 * (size_t)nodes), o_lc = carve(4 * (size_t)R),
                o_ln = carve(4 * cap), o_lj = carve(4 * cap), o_lw = carve(4 * cap), o_sc = carve(8 * (size_t)R),
                o_cr = carve(4 * (size_t)R), o_st = carve(4 * (size_t)R);
@@ -720,6 +730,11 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   CU(h2d(i_po, b->prev_off, 4 * (size_t)(nodes + 1)));
   CU(h2d(i_pj, b->prev_job, 4 * (size_t)prevs));
   CU(h2d(i_pw, b->prev_workers, 4 * (size_t)prevs));
+  if (pods) {
+    CU(h2d(i_qo, b->pods_off, 4 * (size_t)(reqs + 1)));
+    CU(h2d(i_qn, b->pods_node, 4 * (size_t)podRuns));
+    CU(h2d(i_qs, b->pods_slots, 4 * (size_t)podRuns));
+  }
   PlaceArgs a{};
   a.rounds = R;
   a.node_off = (const int32_t*)(base + i_no); a.node_slots = (const int32_t*)(base + i_ns);
@@ -727,6 +742,11 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   a.prev_off = (const int32_t*)(base + i_po); a.prev_job = (const int32_t*)(base + i_pj);
   a.prev_workers = (const int32_t*)(base + i_pw);
   a.max_nodes = max_nodes; a.max_requests = max_req;
+  if (pods) {
+    a.pods_off = (const int32_t*)(base + i_qo); a.pods_node = (const int32_t*)(base + i_qn);
+    a.pods_slots = (const int32_t*)(base + i_qs);
+    a.migrated_workers = (int32_t*)(base + o_mw); a.migrated_launchers = (int32_t*)(base + o_ml);
+  }
   a.phys_of_logical = (int32_t*)(base + o_ph); a.free_slots = (int32_t*)(base + o_fr); a.lay_cnt = (int32_t*)(base + o_lc);
   a.lay_node = (int32_t*)(base + o_ln); a.lay_job = (int32_t*)(base + o_lj); a.lay_workers = (int32_t*)(base + o_lw);
   a.score = (long long*)(base + o_sc); a.cross = (int32_t*)(base + o_cr); a.status = (int32_t*)(base + o_st);
@@ -744,6 +764,10 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   CU(d2h(o->score, o_sc, 8 * (size_t)R));
   CU(d2h(o->cross, o_cr, 4 * (size_t)R));
   CU(d2h(o->status, o_st, 4 * (size_t)R));
+  if (pods) {
+    CU(d2h(o->migrated_workers, o_mw, 4 * (size_t)R));
+    CU(d2h(o->migrated_launchers, o_ml, 4 * (size_t)R));
+  }
   CU(cudaStreamSynchronize(s));
   return VODA_OK;
 }

@@ -53,6 +53,11 @@ struct PlaceArgs {
   const int32_t* prev_job;
   const int32_t* prev_workers;
   int32_t max_nodes, max_requests;
+  const int32_t* pods_off;  // optional pod -> node table (run-length per request), see voda_accel.h
+  const int32_t* pods_node;
+  const int32_t* pods_slots;
+  int32_t* migrated_workers;  // optional outputs
+  int32_t* migrated_launchers;
   int32_t* phys_of_logical;
   int32_t* free_slots;
   int32_t* lay_cnt;

@@ -76,6 +76,11 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
       sm.red[0] = VODA_ST_OK;  // status
       sm.red[1] = 0;           // entries
       sm.red[2] = 0;           // cross
+      sm.red[3] = 0;           // two 32-bit counters: migrated workers, migrated launchers
+      if (a.migrated_workers) {
+        a.migrated_workers[rd] = 0;
+        a.migrated_launchers[rd] = 0;
+      }
     }
     if (n <= 0) {  // no nodes: bestFit returns at once, size-0 matrix
       if (tid == 0) {
@@ -290,6 +295,54 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
         a.lay_cnt[rd] = cnt;
         a.cross[rd] = (int)sm.red[2];
         a.status[rd] = VODA_ST_OK;
+      }
+    }
+    // ---- updateJobStates + updatePodNodeName (:548-617) as counts: which worker pods change node ----
+    // A job's new nodeNumSlotsList = its layout entries renamed to their physical nodes, taken by
+    // physical index; its old one is the caller's run-length pod table.  Pod i of the job sits on
+    // the i-th slot of either list; a pod present in both whose node differs is deleted (:589-596),
+    // and a job all of whose workers are deleted loses its launcher too (:606-609).
+    if (a.pods_off) {
+      __syncthreads();  // the binding (starCol) is final
+      int* mig = reinterpret_cast<int*>(&sm.red[3]);
+      for (int job = tid; job < m; job += kThreads) {
+        if (sm.jobHead[job] < 0) continue;  // no entry: the job is not in the new jobStates
+        int run = a.pods_off[q0 + job];
+        const int runEnd = a.pods_off[q0 + job + 1];
+        int left = run < runEnd ? a.pods_slots[run] : 0;
+        int last = -1, deleted = 0, numWorkers = 0;
+        for (;;) {
+          int best = 0x7fffffff, bw = 0;
+          for (int e = sm.jobHead[job]; e >= 0; e = sm.eNext[e]) {
+            const int p = sm.mk.starCol[sm.eNode[e]];
+            if (p > last && p <= best) {  // '<=': a later entry on the same node overwrites (map assignment)
+              best = p;
+              bw = sm.eW[e];
+            }
+          }
+          if (best == 0x7fffffff) break;
+          last = best;
+          numWorkers += bw;
+          int w = bw;
+          while (w > 0) {
+            while (run < runEnd && left <= 0) {
+              run++;
+              left = run < runEnd ? a.pods_slots[run] : 0;
+            }
+            if (run >= runEnd) break;  // the remaining pods are new: nothing to delete
+            const int take = w < left ? w : left;
+            if (a.pods_node[run] != best) deleted += take;
+            w -= take;
+            left -= take;
+          }
+        }
+        if (deleted) atomicAdd(&mig[0], deleted);
+        if (deleted == numWorkers) atomicAdd(&mig[1], 1);
+      }
+      __syncthreads();
+      if (tid == 0) {
+        a.migrated_workers[rd] = mig[0];
+        a.migrated_launchers[rd] = mig[1];
       }
     }
   }
