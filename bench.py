@@ -76,10 +76,10 @@ WORKLOADS = {
                              "ready jobs (870 GPUs) -> bestFit + score + munkres on 128 nodes x 8 slots "
                              "(resched(), scheduler.go:326-364)"),
     # configs[4]
-    "replay_c5": dict(kind="replay", replicas=8, rounds=12500, nodes=128, slots=8, steps=1,
-                      desc="Synthetic Philly-like trace replay, Elastic-SRJF + placement on 128 nodes x 8 GPUs: 8 what-if "
-                           "replicas x 12.5k jobs per GPU = 100k jobs per GPU (BASELINE configs[4]; --rounds sets jobs per "
-                           "replica; profiles/ holds the 64 x 100k-job run)"),
+    "replay_c5": dict(kind="replay", replicas=64, rounds=1562, nodes=128, slots=8, steps=1,
+                      desc="Synthetic Philly-like trace replay, Elastic-SRJF + placement on 128 nodes x 8 GPUs: 64 what-if "
+                           "replicas x 1562 jobs = 100k jobs per GPU, replicas sharded over the GPUs (BASELINE configs[4]; "
+                           "--rounds sets jobs per replica)"),
 }
 
 W = synth.W
