@@ -311,11 +311,11 @@ int afsl_hot_columns(const AllocArgs& a, int Jp) {
 // four-warp kernel above.
 static int afsl_warp_columns(const AllocArgs& a, int Jp) {
   // columns of 16-bit ranks (column 0 = rem, w = len(., w)): as many as keep the CTA at about
-  // 31 bytes of shared memory per job slot (seven 1024-job rounds per SM), more for small rounds
+  // 27 bytes of shared memory per job slot (eight 1024-job rounds per SM), more for small rounds
   // (the SM holds at most 32 CTAs anyway), never more than the table is wide
-  long target = 31L * Jp;
+  long target = 27300L * Jp / 1024;
   if (target < 7000) target = 7000;
-  long nc = (target - (long)Jp * 10 - 32) / (2L * (Jp + 32));
+  long nc = (target - (long)Jp * 6 - 32) / (2L * (Jp + 32));
   if (nc < 1) nc = 1;
   if (const char* v = std::getenv("VODA_AFSL_NC")) nc = std::atoi(v);
   if (nc > a.stride) nc = a.stride;
@@ -325,7 +325,7 @@ static int afsl_warp_columns(const AllocArgs& a, int Jp) {
 
 size_t afsl_smem_bytes(const AllocArgs& a) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  if (Jp <= 1024) {
+  if (Jp <= 1024 && a.max_total <= 0xFFFF) {
     const int Jw = Jp < 32 ? 32 : Jp;
     return afslw::smem_bytes(Jw, afsl_warp_columns(a, Jw));
   }
@@ -355,7 +355,7 @@ static cudaError_t launch_afsl_warp(const AllocArgs& a, int sms, cudaStream_t st
 
 cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream) {
   const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
-  const bool warp = true;
+  const bool warp = a.max_total <= 0xFFFF;  // the one-warp kernel keeps a job's count in 16 bits
   if (warp && Jp <= 32) return launch_afsl_warp<1>(a, sms, stream);
   if (warp && Jp == 64) return launch_afsl_warp<2>(a, sms, stream);
   if (warp && Jp == 128) return launch_afsl_warp<4>(a, sms, stream);

@@ -107,8 +107,9 @@ __device__ __forceinline__ void row_zero(unsigned& bits, int rankA, int rankB, u
 
 struct Smem {
   unsigned short* rankT;  // [NC][pitch], pitch = Jp + 32; entry Jp of a column is the dead slots' flag
-  int32_t* r;             // [Jp] workers per id
-  unsigned* scr;          // [Jp] rank-sort keys, then champion cache / compaction staging
+  unsigned short* r;      // [Jp] workers per id (a job never holds more than min(total, MaxNumProc) <= 65535)
+  unsigned* scr;          // [Jp] rank-sort keys during set-up; afterwards its first half is r[], its second
+                          // half the champion cache, which also stages the compaction (half the positions at a time)
   unsigned short* perm;   // [Jp] id -> job index within the round
   long long* red;         // [2]
   // sort overlay on rankT
@@ -125,7 +126,7 @@ __host__ __device__ inline size_t table_bytes(int Jp, int NC) {
   return (t + 15) & ~(size_t)15;
 }
 __host__ __device__ inline size_t smem_bytes(int Jp, int NC) {
-  return table_bytes(Jp, NC) + (size_t)Jp * (4 + 4 + 2) + 16 + 16;
+  return table_bytes(Jp, NC) + (size_t)Jp * (4 + 2) + 16 + 16;
 }
 
 template <int SLOTS>
@@ -143,8 +144,8 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
     sm.klo = reinterpret_cast<int32_t*>(p + 8 * (size_t)Jp);
     sm.perm32 = reinterpret_cast<int*>(p + 12 * (size_t)Jp);
     p += table_bytes(Jp, NC);
-    sm.r = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Jp;
-    sm.scr = reinterpret_cast<unsigned*>(p); p += 4 * (size_t)Jp;
+    sm.scr = reinterpret_cast<unsigned*>(p);
+    sm.r = reinterpret_cast<unsigned short*>(p); p += 4 * (size_t)Jp;
     sm.perm = reinterpret_cast<unsigned short*>(p);
   }
   const int lane = threadIdx.x;
@@ -230,7 +231,6 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
           Rr[k] = 0.0f;
           remv[k] = 0.0f;
         }
-        sm.r[t] = 0;
       }
       maxmax = __reduce_max_sync(full, maxmax);
       // ---- rank columns: 0 = rem, w = rem / S[w] (afsl.go:94-100), w up to the largest count a
@@ -266,7 +266,16 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
         __syncwarp();
       }
     }
-    unsigned short* champIn = reinterpret_cast<unsigned short*>(sm.scr);  // position of the champion entering a take-over position
+    // r[] and the champion cache take over the sort scratch
+    unsigned short* champIn = sm.r + Jp;  // position of the champion entering a take-over position
+    unsigned* stage = reinterpret_cast<unsigned*>(champIn);  // Jp/2 words: compaction staging
+#pragma unroll
+    for (int k = 0; k < SLOTS; k++) sm.r[32 * k + lane] = 0;
+    if (min(total, max(maxmax, 1)) > 0xFFFF) {  // a count could outgrow 16 bits: not this kernel's shape
+      for (int i = lane; i < n; i += 32) a.out_gpus[o + i] = 0;
+      if (lane == 0) a.out_status[rd] = VODA_ST_BOUND;
+      continue;
+    }
     __syncwarp();
 
     // ---- uniform state (same value in every lane) ------------------------------------------------
@@ -370,7 +379,7 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
       const int sx = cp >> 5, lx = cp & 31;
       __syncwarp();
       const int prevPos = cp > head ? (int)champIn[cp] : -1;
-      if (lane == 0) sm.r[c] = nr;
+      if (lane == 0) sm.r[c] = (unsigned short)nr;
       if (lane == lx) {
         if (removed) {
           a.out_gpus[o + jobc] = nr;
@@ -396,43 +405,52 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
       pos = removed ? cp + 1 : cp;
       // ---- squeeze the dead slots out (uniform condition) ---------------------------------------
       if (__builtin_expect(dead >= kCompactAt || (dead > 0 && dead * 4 >= len), 0)) {
+        unsigned nzero = 0;
         int base = 0;
+        constexpr int kHalf = Jp / 2;  // the staging buffer holds half of the positions
 #pragma unroll
         for (int pass = 0; pass < 3; pass++) {
-          base = 0;
-#pragma unroll
-          for (int k = 0; k < SLOTS; k++) {
-            const bool alive = (aliveBits >> k) & 1u;
-            const unsigned m = __ballot_sync(full, alive);
-            const int dst = base + __popc(m & ltmask);
-            if (alive) {
-              unsigned v;
-              if (pass == 0) v = (unsigned)id[k] | (((zeroBits >> k) & 1u) << 16);
-              else if (pass == 1) v = __float_as_uint(L[k]);
-              else v = __float_as_uint(Rr[k]);
-              sm.scr[dst] = v;
-            }
-            base += __popc(m);
-          }
-          __syncwarp();
           unsigned nz = 0;
 #pragma unroll
-          for (int k = 0; k < SLOTS; k++) {
-            const int p = 32 * k + lane;
-            const bool in = p < base;
-            const unsigned v = in ? sm.scr[p] : 0u;
-            if (pass == 0) {
-              id[k] = in ? (int)(v & 0xFFFFu) : Jp;
-              nz |= (in ? ((v >> 16) & 1u) : 1u) << k;
-            } else if (pass == 1) {
-              L[k] = in ? __uint_as_float(v) : NEG_INF;
-            } else {
-              Rr[k] = in ? __uint_as_float(v) : 0.0f;
+          for (int h = 0; h < 2; h++) {
+            base = 0;
+#pragma unroll
+            for (int k = 0; k < SLOTS; k++) {
+              const bool alive = (aliveBits >> k) & 1u;
+              const unsigned m = __ballot_sync(full, alive);
+              const int dst = base + __popc(m & ltmask);
+              if (alive && dst / kHalf == h) {
+                unsigned v;
+                if (pass == 0) v = (unsigned)id[k] | (((zeroBits >> k) & 1u) << 16);
+                else if (pass == 1) v = __float_as_uint(L[k]);
+                else v = __float_as_uint(Rr[k]);
+                stage[dst - h * kHalf] = v;
+              }
+              base += __popc(m);
             }
+            __syncwarp();
+            // in place: a live element never moves to a later position, so the second half's sources
+            // (positions >= Jp/2) are untouched by the first half's writes; zeroBits is rebuilt aside
+#pragma unroll
+            for (int k = 0; k < SLOTS; k++) {
+              const int p = 32 * k + lane;
+              if (p / kHalf != h) continue;
+              const bool in = p < base;
+              const unsigned v = in ? stage[p - h * kHalf] : 0u;
+              if (pass == 0) {
+                id[k] = in ? (int)(v & 0xFFFFu) : Jp;
+                nz |= (in ? ((v >> 16) & 1u) : 1u) << k;
+              } else if (pass == 1) {
+                L[k] = in ? __uint_as_float(v) : NEG_INF;
+              } else {
+                Rr[k] = in ? __uint_as_float(v) : 0.0f;
+              }
+            }
+            __syncwarp();
           }
-          if (pass == 0) zeroBits = nz;
-          __syncwarp();
+          if (pass == 0) nzero = nz;
         }
+        zeroBits = nzero;
         aliveBits = 0;
 #pragma unroll
         for (int k = 0; k < SLOTS; k++) aliveBits |= (32 * k + lane < base ? 1u : 0u) << k;
