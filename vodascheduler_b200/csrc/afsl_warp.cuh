@@ -73,6 +73,50 @@ __device__ inline void warp_sort_u32(unsigned* key, int P, int lane) {
   }
 }
 
+// Warp-wide bitonic sort of 32 * SLOTS keys held in registers, SLOTS per lane; element e of lane l is
+// item l * SLOTS + e of the network.  Exchanges inside a lane are two min/max instructions on
+// registers, exchanges between lanes one shuffle and one min-or-max; a lane whose block sorts
+// descending in a phase works on the complemented keys instead (no per-exchange direction).
+// About a quarter of the instructions of the same network on shared memory, and no barrier.
+template <int SLOTS>
+__device__ __forceinline__ void warp_sort_regs(unsigned (&v)[SLOTS], int lane) {
+  constexpr int P = 32 * SLOTS;
+#pragma unroll
+  for (int k = 2; k <= P; k <<= 1) {
+    const bool flip = k >= SLOTS && k < P && (lane & (k / SLOTS)) != 0;  // this lane's block is a descending one
+    if (k >= SLOTS) {
+#pragma unroll
+      for (int e = 0; e < SLOTS; e++) v[e] = flip ? ~v[e] : v[e];
+    }
+#pragma unroll
+    for (int j = k >> 1; j >= 1; j >>= 1) {
+      if (j >= SLOTS) {
+        const int partner = j / SLOTS;
+        const bool lower = (lane & partner) == 0;
+#pragma unroll
+        for (int e = 0; e < SLOTS; e++) {
+          const unsigned o = __shfl_xor_sync(0xffffffffu, v[e], partner);
+          v[e] = lower ? min(v[e], o) : max(v[e], o);
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < SLOTS; e++) {
+          if ((e & j) == 0) {
+            const bool asc = k >= SLOTS || (e & k) == 0;  // below SLOTS the direction is a bit of e
+            const unsigned a = v[e], b = v[e | j];
+            v[e] = asc ? min(a, b) : max(a, b);
+            v[e | j] = asc ? max(a, b) : min(a, b);
+          }
+        }
+      }
+    }
+    if (k >= SLOTS) {
+#pragma unroll
+      for (int e = 0; e < SLOTS; e++) v[e] = flip ? ~v[e] : v[e];
+    }
+  }
+}
+
 // One challenger against a champion that holds rc >= 1 workers (afsl.go:80-90), on predicates:
 //   ge = rankA >= rankB   (lenA >= lenB: the challenger is the shorter job)
 //   beat = ge ? !(L_c > Rr_b) : (L_b > Rr_c);   bits |= bit when beat
@@ -204,50 +248,38 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
 #pragma unroll
       for (int k = 0; k < SLOTS; k++) sm.perm[32 * k + lane] = tmp[k];
     }
-    // ---- per-slot registers ---------------------------------------------------------------
-    int id[SLOTS];
-    float L[SLOTS], Rr[SLOTS];
-    unsigned zeroBits = 0xffffffffu;  // bit k: slot k holds a job with 0 workers (dead slots keep the bit)
-    unsigned aliveBits = 0;           // bit k: slot k holds a live job
+    // ---- rank columns: 0 = rem, w = rem / S[w] (afsl.go:94-100), w up to the largest count a
+    //      champion can hold in this round (below the largest MaxNumProc).  Built before the per-slot
+    //      state so that the sort has the registers to itself.
     int maxmax = 0;
     {
       float remv[SLOTS];
 #pragma unroll
       for (int k = 0; k < SLOTS; k++) {
         const int t = 32 * k + lane;
+        remv[k] = 0.0f;
         if (t < n) {
           const int job = sm.perm[t];
-          id[k] = t;
-          const float s0 = S(job, 0), s1 = S(job, 1);
-          const float d = s1 - s0;
-          L[k] = d / s1;
-          Rr[k] = d / s0;
-          aliveBits |= 1u << k;
           remv[k] = remb[job];
           maxmax = max(maxmax, mxb[job]);
-        } else {
-          id[k] = Jp;
-          L[k] = NEG_INF;
-          Rr[k] = 0.0f;
-          remv[k] = 0.0f;
         }
       }
       maxmax = __reduce_max_sync(full, maxmax);
-      // ---- rank columns: 0 = rem, w = rem / S[w] (afsl.go:94-100), w up to the largest count a
-      //      champion can hold in this round (below the largest MaxNumProc)
       const int cols = min(NC, max(1, maxmax));
       for (int c = 0; c < cols; c++) {
-        unsigned key[SLOTS];
+        unsigned key[SLOTS], srt[SLOTS];
 #pragma unroll
         for (int k = 0; k < SLOTS; k++) {
           const int t = 32 * k + lane;
           float v = remv[k];
           if (c > 0 && t < n) v = v / S(sm.perm[t], c);
           key[k] = t < n ? rank_key(v) : 0xFFFFFFFFu;
-          sm.scr[t] = key[k];
+          srt[k] = key[k];
         }
+        warp_sort_regs<SLOTS>(srt, lane);
+#pragma unroll
+        for (int k = 0; k < SLOTS; k++) sm.scr[lane * SLOTS + k] = srt[k];
         __syncwarp();
-        warp_sort_u32(sm.scr, Jp, lane);
         // rank = number of keys below mine (lower bound in the sorted keys)
         int lb[SLOTS];
 #pragma unroll
@@ -264,6 +296,28 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
           col[32 * k + lane] = key[k] == 0xFFFFFFFFu ? (unsigned short)kNanRank : (unsigned short)lb[k];
         if (lane == 0) col[Jp] = (unsigned short)kNanRank;
         __syncwarp();
+      }
+    }
+    // ---- per-slot registers ---------------------------------------------------------------
+    int id[SLOTS];
+    float L[SLOTS], Rr[SLOTS];
+    unsigned zeroBits = 0xffffffffu;  // bit k: slot k holds a job with 0 workers (dead slots keep the bit)
+    unsigned aliveBits = 0;           // bit k: slot k holds a live job
+#pragma unroll
+    for (int k = 0; k < SLOTS; k++) {
+      const int t = 32 * k + lane;
+      if (t < n) {
+        const int job = sm.perm[t];
+        id[k] = t;
+        const float s0 = S(job, 0), s1 = S(job, 1);
+        const float d = s1 - s0;
+        L[k] = d / s1;
+        Rr[k] = d / s0;
+        aliveBits |= 1u << k;
+      } else {
+        id[k] = Jp;
+        L[k] = NEG_INF;
+        Rr[k] = 0.0f;
       }
     }
     // r[] and the champion cache take over the sort scratch
