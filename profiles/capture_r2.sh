@@ -10,7 +10,7 @@ NCU="ncu --clock-control none"
 # outside the timed region and would fill the list)
 for wl in afsl_c3 tiresias_c1 ffdl_c2 munkres_c4 alloc_place; do
   python bench.py --workload $wl --only-headline --steps 2 --warmup 3 --e2e-steps 1 --no-cpu > gpurun_out/r2_plain_$wl.json 2> gpurun_out/r2_plain_$wl.err || { echo "plain $wl failed"; continue; }
-  $NCU --metrics gpu__time_duration.sum -k "regex:voda|afslw" -c 400 --csv --log-file gpurun_out/r2_launches_$wl.csv \
+  $NCU --metrics gpu__time_duration.sum -k "regex:^(afsl|tiresias|ffdl|fill|munkres|place|curves|tick|compare)" -c 400 --csv --log-file gpurun_out/r2_launches_$wl.csv \
       python bench.py --workload $wl --only-headline --steps 2 --warmup 3 --e2e-steps 1 --no-cpu > /dev/null 2>&1
 done
 cap() {  # name, kernel regex, workload, launch-skip
@@ -21,7 +21,7 @@ cap afsl afsl_warp_kernel afsl_c3 3
 cap tiresias tiresias_kernel tiresias_c1 3
 cap ffdl_dp ffdl_dp_kernel ffdl_c2 3
 cap ffdl_bt ffdl_backtrack_kernel ffdl_c2 3
-cap munkres 'munkres_kernel<unsigned' munkres_c4 3
+cap munkres munkres_kernel munkres_c4 4   # launch 4 = the uint8 pass of the second step's ladder
 cap place place_kernel alloc_place 3
 cap fill fill_kernel alloc_place 3
 ls -la gpurun_out | tail -30

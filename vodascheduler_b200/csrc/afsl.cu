@@ -332,8 +332,10 @@ size_t afsl_smem_bytes(const AllocArgs& a) {
   return afsl_fixed_smem(Jp) + (size_t)afsl_hot_columns(a, Jp) * 4 * (size_t)Jp;
 }
 
+// Resident CTAs per SM of the one-warp kernel for this shape (a round is one long dependent chain, so a
+// launch takes as long as its fullest CTA: batches are best cut into multiples of sms * this).
 template <int SLOTS>
-static cudaError_t launch_afsl_warp(const AllocArgs& a, int sms, cudaStream_t stream) {
+static cudaError_t afsl_warp_residency(const AllocArgs& a, int* perSm, size_t* smemOut, int* ncOut) {
   const int Jp = 32 * SLOTS;
   const int NC = afsl_warp_columns(a, Jp);
   const size_t smem = afslw::smem_bytes(Jp, NC);
@@ -342,15 +344,38 @@ static cudaError_t launch_afsl_warp(const AllocArgs& a, int sms, cudaStream_t st
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  int perSm = 0;
-  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, kern, 32, smem);
+  cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(perSm, kern, 32, smem);
   if (e != cudaSuccess) return e;
-  if (perSm < 1) perSm = 1;
-  if (const char* v = std::getenv("VODA_AFSL_CTAS")) perSm = std::max(1, std::min(perSm, std::atoi(v)));
+  if (*perSm < 1) *perSm = 1;
+  if (const char* v = std::getenv("VODA_AFSL_CTAS")) *perSm = std::max(1, std::min(*perSm, std::atoi(v)));
+  if (smemOut) *smemOut = smem;
+  if (ncOut) *ncOut = NC;
+  return cudaSuccess;
+}
+
+template <int SLOTS>
+static cudaError_t launch_afsl_warp(const AllocArgs& a, int sms, cudaStream_t stream) {
+  int perSm = 0, NC = 0;
+  size_t smem = 0;
+  cudaError_t e = afsl_warp_residency<SLOTS>(a, &perSm, &smem, &NC);
+  if (e != cudaSuccess) return e;
   int grid = sms * perSm;
   if (a.rounds < grid) grid = a.rounds;
-  kern<<<grid, 32, smem, stream>>>(a, NC);
+  afslw::afsl_warp_kernel<SLOTS><<<grid, 32, smem, stream>>>(a, NC);
   return cudaGetLastError();
+}
+
+int afsl_wave_rounds(const AllocArgs& a, int sms) {
+  const int Jp = next_pow2(a.max_jobs > 0 ? a.max_jobs : 1);
+  if (a.max_total > 0xFFFF || Jp > 1024) return 0;
+  int perSm = 0;
+  cudaError_t e = Jp <= 32    ? afsl_warp_residency<1>(a, &perSm, nullptr, nullptr)
+                  : Jp == 64  ? afsl_warp_residency<2>(a, &perSm, nullptr, nullptr)
+                  : Jp == 128 ? afsl_warp_residency<4>(a, &perSm, nullptr, nullptr)
+                  : Jp == 256 ? afsl_warp_residency<8>(a, &perSm, nullptr, nullptr)
+                  : Jp == 512 ? afsl_warp_residency<16>(a, &perSm, nullptr, nullptr)
+                              : afsl_warp_residency<32>(a, &perSm, nullptr, nullptr);
+  return e == cudaSuccess ? sms * perSm : 0;
 }
 
 cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream) {

@@ -445,6 +445,15 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
   const size_t total_bytes = per_job * (size_t)off[R] + 12 * (size_t)R;
   const size_t bytes_per_round = std::max<size_t>(1, total_bytes / (size_t)R);
   size_t rounds_per_sz = std::max<size_t>((size_t)ctx->sms * 12, ((size_t)16 << 20) / bytes_per_round + 1);
+  if (b->algo == VODA_ALGO_AFSL) {
+    // an AFS-L round is one long dependent chain: a chunk that is not a whole number of waves of the
+    // launch leaves SMs idle for a full round's time
+    AllocArgs probe = make_args(b);
+    probe.max_jobs = max_jobs;
+    probe.max_total = max_total;
+    const size_t wave = (size_t)afsl_wave_rounds(probe, ctx->sms);
+    if (wave > 0) rounds_per_sz = std::max<size_t>(1, rounds_per_sz / wave) * wave;  // rounded down: the first chunk's copy is exposed
+  }
   if (rounds_per_sz > (size_t)R) rounds_per_sz = (size_t)R;
   const int rounds_per = (int)rounds_per_sz;
   ctx->h2d_bytes = 0;

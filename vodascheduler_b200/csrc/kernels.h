@@ -24,6 +24,8 @@ cudaError_t launch_tiresias(const AllocArgs& a, int sms, cudaStream_t stream);
 // AFS-L (afsl.cu)
 size_t afsl_smem_bytes(const AllocArgs& a);
 cudaError_t launch_afsl(const AllocArgs& a, int sms, cudaStream_t stream);
+// rounds one full wave of the launch processes (0: no preference); host batches are cut into multiples
+int afsl_wave_rounds(const AllocArgs& a, int sms);
 
 // batched ComputeMunkresMax (munkres.cu)
 size_t munkres_scratch_bytes(int n, int batch, int sms);
