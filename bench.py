@@ -577,12 +577,19 @@ def run_replay(name, wl, ctx, env, steps, warmup, e2e_steps, with_cpu):
     import torch
     from vodascheduler_b200 import replay as rp
     reps = rp.make_replicas(wl["replicas"], wl["rounds"], wl["nodes"], wl["slots"], first=env.rank * wl["replicas"])
-    rp.replay(rp.make_replicas(2, 200, 8, 8), ctx)  # warm-up: kernels loaded, staging buffers grown
+    from vodascheduler_b200 import Context
+    K = wl.get("contexts", 4)  # replica groups, each on its own context (stream) and host thread
+    ctxs = [ctx] + [Context(env.local) for _ in range(K - 1)]
+    for c in ctxs:
+        rp.replay(rp.make_replicas(2, 200, 8, 8), c)  # warm-up: kernels loaded, staging buffers grown
     env.barrier()
-    l0 = ctx.launches
+    l0 = sum(c.launches for c in ctxs)
     t0 = time.perf_counter()
-    stats = rp.replay(reps, ctx)
+    stats = rp.replay_parallel(reps, ctxs, host_threads=max(1, env.threads // (K * env.world)))
     dt = time.perf_counter() - t0
+    launches = sum(c.launches for c in ctxs) - l0
+    for c in ctxs[1:]:
+        c.close()
     t = torch.tensor([dt, float(stats["rounds"])], dtype=torch.float64, device=env.dev)
     if env.world > 1:
         tm = t.clone()
@@ -607,11 +614,12 @@ def run_replay(name, wl, ctx, env, steps, warmup, e2e_steps, with_cpu):
         return None
     val = rounds / dt
     return {"workload": wl["desc"], "value": val, "unit": "rounds/s", "ms_per_step": 1e3 * dt, "steps": 1,
-            "replicas_per_gpu": wl["replicas"], "jobs_per_replica": wl["rounds"],
-            "parallelism": "replicas only (a trace is sequential in time)",
+            "replicas_per_gpu": wl["replicas"], "jobs_per_replica": wl["rounds"], "contexts_per_gpu": K,
+            "parallelism": "replicas only (a trace is sequential in time); the replicas of a GPU are dealt to "
+                           f"{K} contexts, one host thread each",
             "e2e": {"value": val, "unit": "rounds/s", "h2d_bytes_per_step": None, "d2h_bytes_per_step": None,
                     "note": "every tick copies its rounds to the device and the results back; host bookkeeping included"},
-            "gpu_launches": int(ctx.launches - l0), "roofline": None,
+            "gpu_launches": int(launches), "roofline": None,
             "cpu_baseline": {"value": ref["rounds"] / cpu_dt, "unit": "rounds/s", "cores": 1, "kind": "port",
                              "sample": f"one replica of {nchk} jobs through oracle/replay.py (dense allocation port + placement "
                                        f"port + Python bookkeeping restatement), 1 thread"} if with_cpu else None,
@@ -653,6 +661,17 @@ def run_reference(args, name, wl, rank):
         "e2e": {"value": val, "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference Go timing unavailable: no Go toolchain on this image; this is oracle/ (C++ restatement)",
     }))
+
+
+def release(ctx):
+    """Between workloads: page-locked host buffers and cached device memory go back (eight ranks on one
+    box would otherwise hold ~7 GB of pinned memory each by the end of the run)."""
+    import gc
+    import torch
+    ctx.sync()
+    ctx.free_pinned()
+    gc.collect()
+    torch.cuda.empty_cache()
 
 
 def config_of(name, wl, world):
@@ -705,6 +724,7 @@ def main():
     t_wall0 = time.time()
     head = RUNNERS[wl["kind"]](name, wl, ctx, env, steps, args.warmup, args.e2e_steps or wl.get("e2e_steps", 4), with_cpu)
     t_wall1 = time.time()
+    release(ctx)
     clocks = sampler.stop(t_wall0, t_wall1)
 
     per = {}
@@ -713,6 +733,7 @@ def main():
             pw = dict(WORKLOADS[pn])
             try:
                 per[pn] = RUNNERS[pw["kind"]](pn, pw, ctx, env, pw.get("steps", 10), 3, pw.get("e2e_steps", 4), with_cpu)
+                release(ctx)
             except SystemExit:
                 raise
             except Exception as e:  # a per-config failure must not hide the headline

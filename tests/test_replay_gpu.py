@@ -99,3 +99,18 @@ def test_placement_manager_equals_bookkeeping_oracle(ctx, oracle):
             assert dict(nd.jobNumWorkers) == ref.nodeStates[c].jobNumWorkers and nd.freeSlots == ref.nodeStates[c].freeSlots
         assert {j: [(int(x.node[1:]), x.numSlots) for x in js.nodeNumSlotsList] for j, js in pm.jobStates.items()} == \
                {j: [tuple(e) for e in js.nodeNumSlotsList] for j, js in ref.jobStates.items()}
+
+
+def test_replay_parallel_contexts_equal_single(ctx):
+    """Replicas dealt to several contexts (one host thread each) give the per-replica results of one
+    context, in the same order."""
+    from vodascheduler_b200 import Context
+    reps = rp.make_replicas(7, jobs=100, nodes=8, slots=8)
+    one = rp.replay(reps, ctx)
+    extra = [Context(0) for _ in range(2)]
+    try:
+        par = rp.replay_parallel(reps, [ctx] + extra)
+    finally:
+        for c in extra:
+            c.close()
+    assert par["replicas"] == one["replicas"] and par["rounds"] == one["rounds"]

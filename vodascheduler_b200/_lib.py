@@ -209,6 +209,13 @@ class Context:
         self._pins.append(p)
         return arr
 
+    def free_pinned(self):
+        """Give back every buffer handed out by pinned() / pin_batch(); the arrays must not be used
+        afterwards."""
+        for p in getattr(self, "_pins", []):
+            self._lib.voda_host_free(p)
+        self._pins = []
+
     def pin_batch(self, batch: AllocBatch) -> AllocBatch:
         """Copy of `batch` whose arrays live in page-locked memory."""
         from .batch import _ALLOC_ARRAYS

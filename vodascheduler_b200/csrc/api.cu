@@ -712,6 +712,7 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   }
   // placement batches are small (a few KB per round): one staged copy, one kernel
   cudaStream_t s = ctx->pipe[0];
+  PipeGuard guard(ctx);  // an error return below first waits for what is already in flight
   size_t pos = 0;
   auto carve = [&](size_t bytes) { size_t at = pos; pos += align256(bytes ? bytes : 1); return at; };
   const size_t cap = (size_t)nodes + (size_t)reqs;
@@ -778,6 +779,7 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
     CU(d2h(o->migrated_launchers, o_ml, 4 * (size_t)R));
   }
   CU(cudaStreamSynchronize(s));
+  guard.armed = false;
   return VODA_OK;
 }
 
@@ -811,6 +813,7 @@ int voda_build_curves(voda_ctx* ctx, const voda_curve_batch* b, double* out_time
   if (recs > 0 && (!b->workers || !b->epoch_time_sec)) return fail(ctx, VODA_E_INVALID, "null record arrays");
   CU(cudaSetDevice(ctx->device));
   cudaStream_t s = ctx->pipe[0];
+  PipeGuard guard(ctx);  // an error return below first waits for what is already in flight
   const size_t o_off = 0, o_w = align256(4 * (J + 1)), o_t = o_w + align256(4 * recs), o_et = o_t + align256(8 * recs),
                o_sp = o_et + align256(8 * J * W), o_ef = o_sp + align256(8 * J * W), o_st = o_ef + align256(8 * J * W),
                total = o_st + align256(4 * J);
@@ -831,6 +834,7 @@ int voda_build_curves(voda_ctx* ctx, const voda_curve_batch* b, double* out_time
   CU(cudaMemcpyAsync(out_eff, base + o_ef, 8 * J * W, cudaMemcpyDeviceToHost, s));
   CU(cudaMemcpyAsync(out_status, base + o_st, 4 * J, cudaMemcpyDeviceToHost, s));
   CU(cudaStreamSynchronize(s));
+  guard.armed = false;
   return VODA_OK;
 }
 
@@ -884,6 +888,7 @@ int voda_tick(voda_ctx* ctx, const voda_tick_batch* b) {
   if (rc || b->jobs == 0) return rc;
   CU(cudaSetDevice(ctx->device));
   cudaStream_t s = ctx->pipe[0];
+  PipeGuard guard(ctx);  // an error return below first waits for what is already in flight
   const size_t J = (size_t)b->jobs, a4 = align256(4 * J), a8 = align256(8 * J);
   rc = ensure(ctx, ctx->stage[0], 4 * a4 + 8 * a8, s);
   if (rc) return rc;
@@ -917,6 +922,7 @@ int voda_tick(voda_ctx* ctx, const voda_tick_batch* b) {
   CU(cudaMemcpyAsync(b->changed, d4[3], 4 * J, cudaMemcpyDeviceToHost, s));
   for (int i = 0; i < 8; i++) CU(cudaMemcpyAsync(h8[i], d8[i], 8 * J, cudaMemcpyDeviceToHost, s));
   CU(cudaStreamSynchronize(s));
+  guard.armed = false;
   return VODA_OK;
 }
 
@@ -940,6 +946,7 @@ int voda_compare_results(voda_ctx* ctx, int32_t jobs, const int32_t* old_gpu, co
   if (!old_gpu || !new_gpu || !status || !action) return fail(ctx, VODA_E_INVALID, "null buffer");
   CU(cudaSetDevice(ctx->device));
   cudaStream_t s = ctx->pipe[0];
+  PipeGuard guard(ctx);  // an error return below first waits for what is already in flight
   const size_t J = (size_t)jobs, a4 = align256(4 * J);
   int rc = ensure(ctx, ctx->stage[0], 4 * a4, s);
   if (rc) return rc;
@@ -952,6 +959,7 @@ int voda_compare_results(voda_ctx* ctx, int32_t jobs, const int32_t* old_gpu, co
   ctx->launches += 1;
   CU(cudaMemcpyAsync(action, base + 3 * a4, 4 * J, cudaMemcpyDeviceToHost, s));
   CU(cudaStreamSynchronize(s));
+  guard.armed = false;
   return VODA_OK;
 }
 

@@ -122,3 +122,34 @@ def replay(replicas: List[Replica], ctx, max_ticks: int = 0, host_threads: int =
                  history=int(o["history"][k]))
             for k, r in enumerate(replicas)]
     return dict(ticks=int(ticks[0]), rounds=int(o["rounds"][:R].sum()), replicas=reps)
+
+
+def replay_parallel(replicas: List[Replica], contexts, max_ticks: int = 0, host_threads: int = 0):
+    """The same replay with the replicas dealt round-robin to several contexts of one GPU, one host
+    thread per context (ctypes releases the GIL during voda_replay): while one group waits for its
+    kernels another does its bookkeeping.  Replicas are independent, so the per-replica results are
+    those of replay(); they come back in the order of `replicas`."""
+    import threading
+    K = max(1, min(len(contexts), len(replicas)))
+    out: list = [None] * K
+    err: list = [None] * K
+
+    def work(i):
+        try:
+            out[i] = replay(replicas[i::K], contexts[i], max_ticks, host_threads)
+        except Exception as e:  # surfaced below
+            err[i] = e
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(K)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    for e in err:
+        if e is not None:
+            raise e
+    reps = [None] * len(replicas)
+    for i in range(K):
+        for j, r in enumerate(out[i]["replicas"]):
+            reps[i + j * K] = r
+    return dict(ticks=max(o["ticks"] for o in out), rounds=sum(o["rounds"] for o in out), replicas=reps)
