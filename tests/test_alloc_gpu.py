@@ -318,3 +318,27 @@ def test_afsl_large_worker_counts(ctx, oracle):
     b = synth.jobs_batch("AFS-L", rounds=8, jobs_per_round=700, total_gpu=9000)
     b.max_proc = np.where(np.arange(b.jobs) % 7 == 0, 60, b.max_proc).astype(np.int32)
     _same(ctx, oracle, b)
+
+
+@pytest.mark.parametrize("jobs,total", [(40, 90), (300, 700), (1024, 2500)])
+def test_afsl_degenerate_tables_and_times(ctx, oracle, jobs, total):
+    """Quotients that are +Inf, NaN or negative: all-zero speedup rows (rem / 0 = +Inf, 0 / 0 = NaN),
+    zero and negative remaining times, negative and flat table entries, -0.0.  The rank columns must
+    order them exactly as the float32 compares of afsl.go:77-90 do (NaN loses every '>=')."""
+    b = synth.jobs_batch("AFS-L", rounds=10, jobs_per_round=jobs, total_gpu=total)
+    S = b.speedup.reshape(b.jobs, b.speedup_stride).copy()
+    rem = b.remaining_sec.copy()
+    kind = np.arange(b.jobs) % 11
+    S[kind == 0, :] = 0.0                       # every length +Inf (or NaN with rem 0), every ratio NaN
+    S[kind == 1, 1::2] = -0.0
+    S[kind == 2, 1:] = -np.abs(S[kind == 2, 1:])  # negative lengths
+    S[kind == 3, 1:] = 1.0                      # flat: zero gains
+    S[kind == 4, 3:] = 0.0                      # the table ends early
+    rem[kind == 5] = 0.0
+    rem[kind == 6] = -7.5
+    rem[(kind == 0) & (np.arange(b.jobs) % 2 == 0)] = 0.0   # 0 / 0
+    rem[kind == 7] = np.float32(np.inf)
+    b.speedup = S.reshape(-1).astype(np.float32)
+    b.remaining_sec = rem.astype(np.float32)
+    _same(ctx, oracle, b)
+    _same(ctx, oracle, b, dense=False, threads=8)
