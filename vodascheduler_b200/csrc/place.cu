@@ -363,6 +363,7 @@ static int place_grid(const PlaceArgs& a, int sms, size_t smem, cudaError_t* err
   int perSm = 0;
   *err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, place_kernel, kThreads, smem);
   if (perSm < 1) perSm = 1;
+  if (const char* v = std::getenv("VODA_PLACE_CTAS")) perSm = std::max(1, std::min(perSm, std::atoi(v)));
   int grid = sms * perSm;
   if (a.rounds < grid) grid = a.rounds;
   return grid;
