@@ -656,7 +656,7 @@ def run_reference(args, name, wl, rank):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": config_of(name, wl, 1),
+        "config": config_of(name, wl, max(1, args.gpus)),
         "cpu_baseline": {"value": val, "unit": "rounds/s", "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "rounds/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference Go timing unavailable: no Go toolchain on this image; this is oracle/ (C++ restatement)",
@@ -675,8 +675,15 @@ def release(ctx):
 
 
 def config_of(name, wl, world):
-    return {"workload": wl["desc"], "name": name, "rounds_per_gpu": wl["rounds"],
-            "parallelism": f"rounds sharded over {world} GPU(s), no collective on the data path"}
+    """The same dictionary in both arms (ours and --impl reference) for the same command line."""
+    cfg = {"workload": wl["desc"], "name": name, "rounds_per_gpu": wl["rounds"],
+           "parallelism": f"rounds sharded over {world} GPU(s), no collective on the data path"}
+    if wl["kind"] == "alloc":
+        # every array of the synthetic batch: 44 bytes of scalars + the W-entry float32 curve per job
+        mb = (wl["rounds"] * wl["jobs"] * (44 + 4 * W) + 8 * wl["rounds"]) / 1e6
+        cfg["l2"] = (f"inputs {mb:.0f} MB per GPU vs 126 MB L2: every step re-reads them from HBM" if mb > 130
+                     else f"inputs {mb:.0f} MB per GPU (fit L2; outputs are rewritten every step)")
+    return cfg
 
 
 def main():
@@ -744,7 +751,7 @@ def main():
             "metric": "alloc+placement rounds/sec", "value": head["value"], "unit": head["unit"], "n_gpus": world,
             "steps": steps, "warmup": args.warmup, "ms_per_step": head["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(config_of(name, wl, world), l2=head.get("l2")),
+            "config": config_of(name, wl, world),
             "e2e": head["e2e"], "gpu_launches": head.get("gpu_launches"),
             "roofline": head.get("roofline"), "cpu_baseline": head.get("cpu_baseline"), "clocks": clocks,
             "verified_vs_oracle": head.get("verified_vs_oracle"), "rank_summaries": head.get("rank_summaries"),
