@@ -356,8 +356,38 @@ def run_alloc(name, wl, ctx, env, steps, warmup, e2e_steps, with_cpu):
             entry["cpu_baseline"] = None
         if name == "tiresias_c1":
             entry["single_round"] = single_round_latency(wl, ctx, inputs, with_cpu)
+    if inputs.speedup is not None and wl["algo"] in ("ElasticTiresias", "FfDLOptimizer", "AFS-L"):
+        pooled = shared_curves_e2e(name, wl, ctx, env, inputs, e2e_steps)
+        if entry is not None:
+            entry["e2e_shared_curves"] = pooled
     del dbatch, d_out, d_st
     return entry
+
+
+def shared_curves_e2e(name, wl, ctx, env, inputs, e2e_steps):
+    """A SEPARATE, labelled end-to-end line (it never replaces `e2e`): the same batch shape as a what-if
+    study over one job set — every round is the jobs of round 0 under its own total and remaining
+    times — with the speedup curves passed once as a pool (voda_alloc_batch.speedup_off) instead of a
+    dense table per round."""
+    from oracle import oracle
+    pooled, _ = synth.share_curves(inputs, want_dense=False)
+    hb = ctx.pin_batch(pooled)
+    R = pooled.rounds
+    h_out = ctx.pinned((pooled.jobs,), np.int32)
+    h_st = ctx.pinned((R,), np.int32)
+    ms = time_host_steps(env, lambda: ctx.allocate(hb, h_out, h_st), e2e_steps)
+    h2d, d2h = ctx.copied_bytes
+    nchk = min(R, 256)
+    g_ref, s_ref = oracle.allocate(pooled.slice_rounds(0, nchk), dense=True, threads=max(1, env.threads // env.world))
+    ok = np.array_equal(h_out[:int(pooled.job_off[nchk])], g_ref) and np.array_equal(h_st[:nchk], s_ref)
+    if not env.all_ok(ok):
+        raise SystemExit(f"{name}: shared-curve result differs from the oracle; no timing reported")
+    (ms,) = env.max_over_ranks(ms)
+    return {"value": R * env.world * e2e_steps / (ms / 1e3), "unit": "rounds/s", "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "ms_per_step": ms / e2e_steps,
+            "workload": "what-if form of the same shape: all rounds over the jobs of round 0, curves passed once as a pool "
+                        "(speedup_off); NOT comparable with `e2e` or the reference arm, which take a dense table per round",
+            "verified_vs_oracle": {"rounds_per_rank": nchk, "ok": True}}
 
 
 def single_round_latency(wl, ctx, inputs, with_cpu):
@@ -756,7 +786,7 @@ def main():
             "roofline": head.get("roofline"), "cpu_baseline": head.get("cpu_baseline"), "clocks": clocks,
             "verified_vs_oracle": head.get("verified_vs_oracle"), "rank_summaries": head.get("rank_summaries"),
         }
-        for k in ("single_round", "replay"):
+        for k in ("single_round", "replay", "e2e_shared_curves"):
             if k in head:
                 out[k] = head[k]
         if per:

@@ -107,6 +107,12 @@ void  voda_host_free(void* p);
  *   speedup      TrainingJob.Info.Speedup as a dense table: speedup[job*stride + g] is the
  *                value under key fmt.Sprint(g); a key the map lacks is 0.0f, and so is every
  *                g outside [0, stride).
+ *   speedup_off  OPTIONAL: the table as a POOL of curves that jobs point into — the curve of job j is
+ *                the stride entries starting at speedup[speedup_off[j]] (an offset in floats), and many
+ *                jobs may share one curve.  What-if rounds are mostly the same jobs under other totals,
+ *                subsets or remaining times (the map TrainingJob.Info.Speedup belongs to the job, not to
+ *                the round): their curves then cross PCIe once per call instead of once per round.
+ *                speedup_len = floats in speedup[].  NULL: the dense layout above.
  * Arrays a policy never reads may be NULL ("inputs per policy").
  */
 typedef struct {
@@ -130,6 +136,8 @@ typedef struct {
                                           elastic_tiresias.go:18-22; negative -> 10          */
   int32_t        max_jobs;             /* upper bound of jobs per round; 0 -> computed       */
   int32_t        max_total_gpu;        /* upper bound of total_gpu;      0 -> computed       */
+  const int32_t* speedup_off;          /* [jobs] or NULL                                     */
+  int64_t        speedup_len;          /* floats in speedup[] when speedup_off is given      */
 } voda_alloc_batch;
 
 /*

@@ -441,7 +441,8 @@ void run_rounds(const voda_alloc_batch* b, int32_t* out_gpus, int32_t* out_statu
       t.Info = std::make_shared<JobInfo>();
       t.Info->EstimatedRemainningTimeSec = b->remaining_sec ? b->remaining_sec[f] : 0.0f;
       if (b->speedup)
-        for (long g = 0; g < W; g++) t.Info->Speedup[Sprint(g)] = b->speedup[(size_t)f * (size_t)W + (size_t)g];
+        for (long g = 0; g < W; g++)  // dense table, or a pool of curves the jobs point into (speedup_off)
+          t.Info->Speedup[Sprint(g)] = b->speedup[(b->speedup_off ? (size_t)b->speedup_off[f] : (size_t)f * (size_t)W) + (size_t)g];
     }
     ReadyJobs input = jobs;  // Schedule mutates its argument; keep names in input order
     Result result;

@@ -35,7 +35,7 @@ struct Round {
   // Info.Speedup[fmt.Sprint(g)]: a key outside the dense table is a map miss => 0
   float S(int i, long g) const {
     if (!b->speedup || g < 0 || g >= W) return 0.0f;
-    return b->speedup[(size_t)(o + i) * (size_t)W + (size_t)g];
+    return b->speedup[(b->speedup_off ? (size_t)b->speedup_off[o + i] : (size_t)(o + i) * (size_t)W) + (size_t)g];
   }
   bool submitBefore(int x, int y) const {
     int64_t sx = b->submit_sec ? b->submit_sec[o + x] : 0, sy = b->submit_sec ? b->submit_sec[o + y] : 0;

@@ -342,3 +342,39 @@ def test_afsl_degenerate_tables_and_times(ctx, oracle, jobs, total):
     b.remaining_sec = rem.astype(np.float32)
     _same(ctx, oracle, b)
     _same(ctx, oracle, b, dense=False, threads=8)
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_shared_curve_pool_equals_dense(ctx, oracle, algo):
+    """voda_alloc_batch.speedup_off: what-if rounds over the same jobs point into ONE pool of curves.
+    Host path (the pool crosses PCIe once, chunks stage offsets) and device path give exactly what the
+    dense table gives, which is what the oracle gives."""
+    import torch
+    b = synth.jobs_batch(algo, rounds=700, jobs_per_round=40, total_gpu=64)
+    b.total_gpu = (np.arange(700) % 97).astype(np.int32)
+    pooled, dense = synth.share_curves(b)
+    g_ref, s_ref = oracle.allocate(dense, dense=True, threads=8)
+    g, s = ctx.allocate(pooled)
+    assert np.array_equal(s, s_ref) and np.array_equal(g, g_ref)
+    gp, sp = oracle.allocate(pooled, dense=True, threads=8)     # the oracle reads the pool the same way
+    assert np.array_equal(sp, s_ref) and np.array_equal(gp, g_ref)
+    dev = torch.device("cuda", 0)
+    db = pooled.to_device(dev)
+    d_g = torch.zeros(pooled.jobs, dtype=torch.int32, device=dev)
+    d_s = torch.full((pooled.rounds,), -1, dtype=torch.int32, device=dev)
+    ctx.allocate_dev(db, d_g, d_s)
+    ctx.sync()
+    assert np.array_equal(d_s.cpu().numpy(), s_ref) and np.array_equal(d_g.cpu().numpy(), g_ref)
+
+
+def test_shared_curve_pool_large_chunks(ctx, oracle):
+    """Enough rounds for several pipeline chunks: every chunk reads the pool copied at the start."""
+    for algo, jobs in (("FfDLOptimizer", 48), ("AFS-L", 64), ("ElasticTiresias", 64)):
+        b = synth.jobs_batch(algo, rounds=30000, jobs_per_round=jobs, total_gpu=40)
+        b.total_gpu = (1 + np.arange(30000) % 80).astype(np.int32)
+        pooled, dense = synth.share_curves(b)
+        g_ref, s_ref = oracle.allocate(dense, dense=True, threads=8)
+        g, s = ctx.allocate(pooled)
+        assert np.array_equal(s, s_ref) and np.array_equal(g, g_ref)
+        h2d, d2h = ctx.copied_bytes
+        assert h2d < dense.nbytes() / 3   # the curves crossed once

@@ -33,6 +33,7 @@ class AllocBatchStruct(C.Structure):
         ("speedup_stride", C.c_int32), ("queue_num", C.c_int32),
         ("compaction_threshold", C.c_int32), ("max_jobs", C.c_int32),
         ("max_total_gpu", C.c_int32),
+        ("speedup_off", C.c_void_p), ("speedup_len", C.c_int64),
     ]
 
 

@@ -227,4 +227,9 @@ class Context:
                 pv = self.pinned(v.shape, dt)
                 pv[...] = v
                 setattr(b, name, pv)
+        so = getattr(batch, "speedup_off", None)
+        if so is not None:
+            pv = self.pinned(so.shape, np.int32)
+            pv[...] = so
+            b.speedup_off = pv
         return b

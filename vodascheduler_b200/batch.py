@@ -44,7 +44,7 @@ class AllocBatch:
     def __init__(self, algo, job_off, total_gpu, *, submit_sec=None, submit_nsec=None,
                  first_sec=None, first_nsec=None, priority=None, num_proc=None, min_proc=None,
                  max_proc=None, remaining_sec=None, speedup=None, speedup_stride=0,
-                 queue_num=0, compaction_threshold=-1, max_jobs=0, max_total_gpu=0):
+                 queue_num=0, compaction_threshold=-1, max_jobs=0, max_total_gpu=0, speedup_off=None):
         if isinstance(algo, str):
             algo = _abi.ALGO_NAMES.index(algo)
         self.algo = int(algo)
@@ -54,6 +54,10 @@ class AllocBatch:
             if v is not None and isinstance(v, (np.ndarray, list, tuple)):
                 v = np.ascontiguousarray(np.asarray(v, dtype=dt).reshape(-1))
             setattr(self, name, v)
+        # optional: the speedup table as a pool of curves, speedup_off[j] = first float of job j's curve
+        self.speedup_off = None if speedup_off is None else (
+            np.ascontiguousarray(np.asarray(speedup_off, dtype=np.int32).reshape(-1))
+            if isinstance(speedup_off, (np.ndarray, list, tuple)) else speedup_off)
         self.speedup_stride = int(speedup_stride)
         self.queue_num = int(queue_num)
         self.compaction_threshold = int(compaction_threshold)
@@ -73,6 +77,9 @@ class AllocBatch:
         s.algo, s.rounds = self.algo, self.rounds
         for name, _ in _ALLOC_ARRAYS:
             setattr(s, name, _ptr(getattr(self, name)))
+        s.speedup_off = _ptr(getattr(self, "speedup_off", None))
+        sp = getattr(self, "speedup", None)
+        s.speedup_len = 0 if sp is None else int(sp.shape[0] if isinstance(sp, np.ndarray) else sp.numel())
         s.speedup_stride = self.speedup_stride
         s.queue_num = self.queue_num
         s.compaction_threshold = self.compaction_threshold
@@ -95,9 +102,13 @@ class AllocBatch:
             if v is None:
                 kw[name] = None
             elif name == "speedup":
-                kw[name] = v[j0 * self.speedup_stride:j1 * self.speedup_stride]
+                # a pool of curves stays whole (the jobs' offsets are sliced); a dense table is cut
+                kw[name] = v if getattr(self, "speedup_off", None) is not None else \
+                    v[j0 * self.speedup_stride:j1 * self.speedup_stride]
             else:
                 kw[name] = v[j0:j1]
+        if getattr(self, "speedup_off", None) is not None:
+            kw["speedup_off"] = self.speedup_off[j0:j1]
         return AllocBatch(self.algo, self.job_off[r0:r1 + 1] - j0, self.total_gpu[r0:r1],
                           speedup_stride=self.speedup_stride, queue_num=self.queue_num,
                           compaction_threshold=self.compaction_threshold,
@@ -120,6 +131,8 @@ class AllocBatch:
         for name, _ in _ALLOC_ARRAYS:
             v = getattr(self, name)
             setattr(b, name, None if v is None else torch.from_numpy(v).to(device))
+        so = getattr(self, "speedup_off", None)
+        b.speedup_off = None if so is None else torch.from_numpy(so).to(device)
         return b
 
     def nbytes(self):

@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(kThreads) afsl_kernel(AllocArgs a, int Jp, int
     __syncthreads();
     auto S = [&](int job, int g) -> float {  // Info.Speedup[fmt.Sprint(g)], map miss => 0
       if (g < 0 || g >= W) return 0.0f;
-      return a.speedup[(size_t)(o + job) * (size_t)W + (size_t)g];
+      return a.speedup[(a.sp_off ? (size_t)a.sp_off[o + job] : (size_t)(o + job) * (size_t)W) + (size_t)g];
     };
     // ---- stable sort by SubmitTime (:42-44), then relabel every job by its sorted position
     for (int i = tid; i < n; i += kThreads) {
@@ -339,7 +339,7 @@ static cudaError_t afsl_warp_residency(const AllocArgs& a, int* perSm, size_t* s
   const int Jp = 32 * SLOTS;
   const int NC = afsl_warp_columns(a, Jp);
   const size_t smem = afslw::smem_bytes(Jp, NC);
-  auto kern = afslw::afsl_warp_kernel<SLOTS>;
+  const void* kern = a.sp_off ? (const void*)afslw::afsl_warp_kernel<SLOTS, true> : (const void*)afslw::afsl_warp_kernel<SLOTS, false>;
   if (smem > 48 * 1024) {
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
@@ -361,7 +361,8 @@ static cudaError_t launch_afsl_warp(const AllocArgs& a, int sms, cudaStream_t st
   if (e != cudaSuccess) return e;
   int grid = sms * perSm;
   if (a.rounds < grid) grid = a.rounds;
-  afslw::afsl_warp_kernel<SLOTS><<<grid, 32, smem, stream>>>(a, NC);
+  if (a.sp_off) afslw::afsl_warp_kernel<SLOTS, true><<<grid, 32, smem, stream>>>(a, NC);
+  else afslw::afsl_warp_kernel<SLOTS, false><<<grid, 32, smem, stream>>>(a, NC);
   return cudaGetLastError();
 }
 

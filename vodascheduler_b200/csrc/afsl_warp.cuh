@@ -173,7 +173,7 @@ __host__ __device__ inline size_t smem_bytes(int Jp, int NC) {
   return table_bytes(Jp, NC) + (size_t)Jp * (4 + 2) + 16 + 16;
 }
 
-template <int SLOTS>
+template <int SLOTS, bool POOL>
 __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
   constexpr int Jp = 32 * SLOTS;
   constexpr int pitch = Jp + 32;
@@ -214,9 +214,12 @@ __global__ void __launch_bounds__(32) afsl_warp_kernel(AllocArgs a, int NC) {
     const float* __restrict__ Sb = a.speedup + (size_t)o * (size_t)W;
     const int32_t* __restrict__ mxb = a.max_proc + o;
     const float* __restrict__ remb = a.remaining_sec + o;
+    // POOL: the table is a pool of curves the jobs point into (voda_alloc_batch.speedup_off); a separate
+    // instantiation, because even a uniform branch in this lookup costs the dense path 10 %
     auto S = [&](int job, int g) -> float {
       if ((unsigned)g >= (unsigned)W) return 0.0f;
-      return Sb[(unsigned)(job * W + g)];
+      if constexpr (POOL) return a.speedup[(size_t)a.sp_off[o + job] + (size_t)g];
+      else return Sb[(unsigned)(job * W + g)];
     };
     // ---- stable sort by SubmitTime (:42-44); ids are sorted positions from here on ---------
     {

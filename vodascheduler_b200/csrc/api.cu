@@ -34,6 +34,8 @@ struct voda_ctx {
   DevBuf scratch;                  // kernel scratch for the main stream
   DevBuf pipe_scratch[2];          // kernel scratch per pipeline slot
   DevBuf stage[2];                 // staged inputs + outputs per pipeline slot
+  DevBuf curves;                   // the curve pool of a speedup_off batch (copied once per call)
+  cudaEvent_t curves_ready = nullptr;
   void* hstage[2] = {nullptr, nullptr};   // pinned host staging per slot (packed speedup rows)
   size_t hstage_cap[2] = {0, 0};
   cudaEvent_t h2d_done[2] = {nullptr, nullptr};  // the slot's host staging has been consumed
@@ -159,6 +161,8 @@ int check_batch(voda_ctx* ctx, const voda_alloc_batch* b) {
   if ((f & F_REM) && !b->remaining_sec) return fail(ctx, VODA_E_INVALID, "policy needs remaining_sec");
   if ((f & F_SPEED) && (!b->speedup || b->speedup_stride < 1))
     return fail(ctx, VODA_E_INVALID, "policy needs the speedup table (stride >= 1)");
+  if ((f & F_SPEED) && b->speedup_off && b->speedup_len < (int64_t)b->speedup_stride)
+    return fail(ctx, VODA_E_INVALID, "speedup_off needs speedup_len (floats in the curve pool)");
   return VODA_OK;
 }
 
@@ -179,6 +183,7 @@ AllocArgs make_args(const voda_alloc_batch* b) {
   a.max_proc = b->max_proc;
   a.remaining_sec = b->remaining_sec;
   a.speedup = b->speedup;
+  a.sp_off = b->speedup_off;
   a.stride = b->speedup_stride;
   a.queue_num = b->queue_num > 0 ? b->queue_num : 2;                       // tiresias.go:24
   a.compaction = b->compaction_threshold >= 0 ? b->compaction_threshold : 10;  // elastic_tiresias.go:21
@@ -293,6 +298,7 @@ int voda_ctx_create(int device, voda_ctx** out) {
     if ((e = cudaStreamCreateWithFlags(&ctx->pipe[i], cudaStreamNonBlocking)) != cudaSuccess) return bail(e, "cudaStreamCreate");
   for (int i = 0; i < 2; i++)
     if ((e = cudaEventCreateWithFlags(&ctx->h2d_done[i], cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
+  if ((e = cudaEventCreateWithFlags(&ctx->curves_ready, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if (const char* v = std::getenv("VODA_PACK_ROWS")) ctx->pack_rows = std::atoi(v) != 0;
   if (const char* v = std::getenv("VODA_NARROW_COLS")) ctx->narrow_cols = std::atoi(v) != 0;
   *out = ctx;
@@ -303,7 +309,9 @@ void voda_ctx_destroy(voda_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaDeviceSynchronize();
-  DevBuf* bufs[] = {&ctx->scratch, &ctx->pipe_scratch[0], &ctx->pipe_scratch[1], &ctx->stage[0], &ctx->stage[1]};
+  DevBuf* bufs[] = {&ctx->scratch, &ctx->pipe_scratch[0], &ctx->pipe_scratch[1], &ctx->stage[0], &ctx->stage[1],
+                    &ctx->curves};
+  if (ctx->curves_ready) cudaEventDestroy(ctx->curves_ready);
   for (DevBuf* b : bufs)
     if (b->p) cudaFree(b->p);
   for (int i = 0; i < 2; i++) {
@@ -438,7 +446,7 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
   if (f & F_MIN) per_job += 4;
   if (f & F_MAX) per_job += 4;
   if (f & F_REM) per_job += 4;
-  per_job += 4 * W;
+  per_job += (b->speedup_off && (f & F_SPEED)) ? 4 : 4 * W;  // a pool of curves: only the offset per job
   // chunking: a chunk must hold enough rounds to occupy every SM (one CTA per round, about a
   // dozen resident CTAs per SM) and at least ~16 MiB so the copies run at PCIe speed; several
   // chunks per batch let the H2D copy of one overlap the kernels of the previous one
@@ -459,6 +467,17 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
   ctx->h2d_bytes = 0;
   ctx->d2h_bytes = 0;
   PipeGuard guard(ctx);  // any error return below first waits for what is already in flight
+  // a pool of shared curves crosses PCIe once per call; the chunks only stage the jobs' offsets
+  const bool pool = (f & F_SPEED) && b->speedup_off != nullptr;
+  if (pool) {
+    rc = ensure(ctx, ctx->curves, 4 * (size_t)b->speedup_len, ctx->pipe[0]);
+    if (rc) return rc;
+    CU(cudaStreamSynchronize(ctx->pipe[1]));  // nothing of an earlier call still reads the old pool
+    CU(cudaMemcpyAsync(ctx->curves.p, b->speedup, 4 * (size_t)b->speedup_len, cudaMemcpyHostToDevice, ctx->pipe[0]));
+    CU(cudaEventRecord(ctx->curves_ready, ctx->pipe[0]));
+    CU(cudaStreamWaitEvent(ctx->pipe[1], ctx->curves_ready, 0));
+    ctx->h2d_bytes += 4 * (int64_t)b->speedup_len;
+  }
   for (int c = 0, r0 = 0; r0 < R; c++, r0 += rounds_per) {
     const int r1 = std::min(R, r0 + rounds_per);
     const int slot = c & 1;
@@ -489,7 +508,7 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     // (hostpack.h).  It cuts the PCIe bytes 2.7x but the strided host gather reads almost as
     // many bytes from host DRAM as the DMA engine would have moved, more slowly: measured
     // 10.1 ms vs 8.4 ms per 10k rounds on the 16-core box, so it is off by default
-    const bool packed = ctx->pack_rows && b->algo == VODA_ALGO_FFDL_OPTIMIZER && W >= 8 && nj > 0;
+    const bool packed = !pool && ctx->pack_rows && b->algo == VODA_ALGO_FFDL_OPTIMIZER && W >= 8 && nj > 0;
     size_t o_spoff = 0, packed_floats = 0, Wc = W;
     bool narrow = false;
     if (packed) {
@@ -517,6 +536,8 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
       copies.push_back({o_spoff, h_off, 4 * (nj + 1)});
       o_sp = carve(4 * packed_floats);
       copies.push_back({o_sp, h_sp, 4 * packed_floats});
+    } else if (pool) {
+      o_spoff = in(b->speedup_off, 4, j0, nj);
     } else if (f & F_SPEED) {
       // Only the leading columns of the speedup table that the policy can index in this chunk
       // cross PCIe: index g never exceeds a bound set by the chunk's largest MaxNumProc (and, for
@@ -567,8 +588,8 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     a.min_proc = (f & F_MIN) ? (const int32_t*)(base + o_mn) : nullptr;
     a.max_proc = (f & F_MAX) ? (const int32_t*)(base + o_mx) : nullptr;
     a.remaining_sec = (f & F_REM) ? (const float*)(base + o_rm) : nullptr;
-    a.speedup = (f & F_SPEED) ? (const float*)(base + o_sp) : nullptr;
-    a.sp_off = packed ? (const int32_t*)(base + o_spoff) : nullptr;
+    a.speedup = pool ? (const float*)ctx->curves.p : (f & F_SPEED) ? (const float*)(base + o_sp) : nullptr;
+    a.sp_off = (packed || pool) ? (const int32_t*)(base + o_spoff) : nullptr;
     a.out_gpus = (int32_t*)(base + o_og);
     a.out_status = (int32_t*)(base + o_os);
     rc = dispatch_alloc(ctx, a, ctx->pipe_scratch[slot], s);

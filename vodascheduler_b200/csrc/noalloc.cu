@@ -102,6 +102,7 @@ extern "C" int voda_ffdl_allocate_static(void* stream, const voda_alloc_batch* b
   a.min_proc = b->min_proc;
   a.max_proc = b->max_proc;
   a.speedup = b->speedup;
+  a.sp_off = b->speedup_off;  // a pool of curves, if the caller uses one
   a.stride = b->speedup_stride;
   a.queue_num = 2;
   a.compaction = 10;

@@ -146,7 +146,8 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
     const bool packedKeys = __syncthreads_and(fits) != 0;
     auto S = [&](int i, int g) -> float {  // Info.Speedup[fmt.Sprint(g)], map miss => 0
       if (g < 0 || g >= W) return 0.0f;
-      return a.speedup[(size_t)(o + i) * (size_t)W + (size_t)g];
+      // dense table, or a pool of curves the jobs point into (voda_alloc_batch.speedup_off)
+      return a.speedup[(a.sp_off ? (size_t)a.sp_off[o + i] : (size_t)(o + i) * (size_t)W) + (size_t)g];
     };
     if (elastic)
       for (int i = tid; i < n; i += nth) sm.gain[i] = S(i, sm.mn[i]) / (float)sm.mn[i];  // :58

@@ -300,3 +300,25 @@ def chain_batch(rounds, nodes, slots, jobs_per_round, seed=SEED, round_base=0, l
                     ab.job_off.astype(np.int64), np.zeros(max(1, ab.jobs), np.int64)[:ab.jobs], prev_off, ent_job, ent_w,
                     max_nodes=nodes, max_requests=J)
     return ab, pb
+
+
+def share_curves(b: AllocBatch, want_dense: bool = True):
+    """The what-if form of a batch: every round is the SAME set of jobs (the jobs of round 0: their
+    speedup curves, sizes and times) under the round's own total and remaining times, with the curves
+    stored ONCE as a pool that all rounds point into (voda_alloc_batch.speedup_off).  Needs rounds of
+    equal size.  Returns (pooled batch, the equivalent dense batch)."""
+    cnt = np.diff(b.job_off)
+    assert (cnt == cnt[0]).all(), "share_curves needs rounds of equal size"
+    J, R, Wd = int(cnt[0]), b.rounds, b.speedup_stride
+    tile = lambda v: None if v is None else np.ascontiguousarray(np.tile(v[:J], R))
+    pool = np.ascontiguousarray(b.speedup[:J * Wd])
+    common = dict(submit_sec=tile(b.submit_sec), submit_nsec=tile(b.submit_nsec), first_sec=tile(b.first_sec),
+                  first_nsec=tile(b.first_nsec), priority=tile(b.priority), num_proc=tile(b.num_proc),
+                  min_proc=tile(b.min_proc), max_proc=tile(b.max_proc), remaining_sec=b.remaining_sec,
+                  speedup_stride=Wd, queue_num=b.queue_num, compaction_threshold=b.compaction_threshold)
+    pooled = AllocBatch(b.algo, b.job_off, b.total_gpu, speedup=pool,
+                        speedup_off=np.tile(np.arange(J, dtype=np.int32) * Wd, R), **common)
+    if not want_dense:
+        return pooled, None
+    dense = AllocBatch(b.algo, b.job_off, b.total_gpu, speedup=np.ascontiguousarray(np.tile(pool, R)), **common)
+    return pooled, dense
