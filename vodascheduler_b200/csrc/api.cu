@@ -561,9 +561,30 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     rc = ensure(ctx, ctx->stage[slot], pos, s);
     if (rc) return rc;
     char* base = (char*)ctx->stage[slot].p;
-    for (const Copy& cp : copies) {
-      CU(cudaMemcpyAsync(base + cp.at, cp.src, cp.bytes, cudaMemcpyHostToDevice, s));
-      ctx->h2d_bytes += (int64_t)cp.bytes;
+    // A small batch — the reference's own use: ONE round per Schedule() call — is latency-bound: a
+    // dozen separate copies cost more than the kernel.  Its arrays are gathered into one page-locked
+    // block with the device layout and cross in ONE copy each way.
+    const bool gathered = R == (int)nr && !packed && !narrow && !pool && pos <= ((size_t)256 << 10);
+    if (gathered) {
+      if (ctx->hstage_cap[slot] < pos) {
+        CU(cudaStreamSynchronize(s));
+        if (ctx->hstage[slot]) CU(cudaFreeHost(ctx->hstage[slot]));
+        ctx->hstage[slot] = nullptr;
+        ctx->hstage_cap[slot] = 0;
+        CU(cudaHostAlloc(&ctx->hstage[slot], (size_t)512 << 10, cudaHostAllocDefault));
+        ctx->hstage_cap[slot] = (size_t)512 << 10;
+      }
+      char* hs = (char*)ctx->hstage[slot];
+      for (const Copy& cp : copies) {
+        std::memcpy(hs + cp.at, cp.src, cp.bytes);
+        ctx->h2d_bytes += (int64_t)cp.bytes;
+      }
+      CU(cudaMemcpyAsync(base, hs, o_og, cudaMemcpyHostToDevice, s));
+    } else {
+      for (const Copy& cp : copies) {
+        CU(cudaMemcpyAsync(base + cp.at, cp.src, cp.bytes, cudaMemcpyHostToDevice, s));
+        ctx->h2d_bytes += (int64_t)cp.bytes;
+      }
     }
     if (narrow) {
       CU(cudaMemcpy2DAsync(base + o_sp, 4 * Wc, b->speedup + (size_t)j0 * W, 4 * W, 4 * Wc, nj,
@@ -594,9 +615,18 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     a.out_status = (int32_t*)(base + o_os);
     rc = dispatch_alloc(ctx, a, ctx->pipe_scratch[slot], s);
     if (rc) return rc;
+    ctx->d2h_bytes += (int64_t)(4 * nj + 4 * nr);
+    if (gathered) {  // outputs come back as one block and are handed out after the wait
+      char* hs = (char*)ctx->hstage[slot];
+      CU(cudaMemcpyAsync(hs + o_og, base + o_og, pos - o_og, cudaMemcpyDeviceToHost, s));
+      CU(cudaStreamSynchronize(s));
+      if (nj) std::memcpy(out_gpus + j0, hs + o_og, 4 * nj);
+      std::memcpy(out_status + r0, hs + o_os, 4 * nr);
+      guard.armed = false;  // the only chunk, and its stream has been waited for
+      return VODA_OK;
+    }
     if (nj) CU(cudaMemcpyAsync(out_gpus + j0, base + o_og, 4 * nj, cudaMemcpyDeviceToHost, s));
     CU(cudaMemcpyAsync(out_status + r0, base + o_os, 4 * nr, cudaMemcpyDeviceToHost, s));
-    ctx->d2h_bytes += (int64_t)(4 * nj + 4 * nr);
   }
   CU(cudaStreamSynchronize(ctx->pipe[0]));
   CU(cudaStreamSynchronize(ctx->pipe[1]));
