@@ -48,7 +48,7 @@ extern "C" {
 #define VODA_ST_NONTERMINATING  7  /* guard: the reference loop would never end (bestFit, placement_manager.go:437-485;
                                       ElasticTiresias greedy loop with MinNumProc == 0, elastic_tiresias.go:136-143:
                                       the pick changes neither the job's count nor the free GPUs nor its gain) */
-#define VODA_ST_BOUND           8  /* round exceeds the max_jobs / max_total_gpu the caller declared */
+#define VODA_ST_BOUND           8  /* round exceeds the max_jobs / max_total_gpu / max_max_proc the caller declared */
 #define VODA_ST_RUNTIME_PANIC   9  /* the Go runtime itself would panic (makeslice with negative total) */
 
 /* ---- policies: the eight names of NewAlgorithmFactory, pkg/algorithm/types.go:26-47 - */
@@ -114,6 +114,13 @@ void  voda_host_free(void* p);
  *                the round): their curves then cross PCIe once per call instead of once per round.
  *                speedup_len = floats in speedup[].  NULL: the dense layout above.
  * Arrays a policy never reads may be NULL ("inputs per policy").
+ *   max_max_proc OPTIONAL, read by the FfDL Optimizer only.  Its dynamic program keeps rows of the
+ *                table P (ffdl_optimizer.go:54-60) in device scratch for the backtrack; when no job
+ *                can take more than 32 GPUs it keeps every fourth row and recomputes the rest.  A
+ *                caller of the _dev / _static entry points who declares the bound (<= 32) lets
+ *                the scratch be SIZED for that: a quarter of the memory per round.  A round
+ *                that breaks a declared bound reports VODA_ST_BOUND.  voda_allocate works the bound
+ *                out from the host arrays itself.
  */
 typedef struct {
   int32_t        algo;                 /* VODA_ALGO_*                                        */
@@ -138,6 +145,9 @@ typedef struct {
   int32_t        max_total_gpu;        /* upper bound of total_gpu;      0 -> computed       */
   const int32_t* speedup_off;          /* [jobs] or NULL                                     */
   int64_t        speedup_len;          /* floats in speedup[] when speedup_off is given      */
+  int32_t        max_max_proc;         /* upper bound of the GPUs one job can take, min(MaxNumProc,
+                                          total_gpu); 0 -> not declared (see below)          */
+  int32_t        reserved0;            /* 0                                                  */
 } voda_alloc_batch;
 
 /*
@@ -166,8 +176,9 @@ int voda_allocate_dev(voda_ctx* ctx, const voda_alloc_batch* dev_batch,
  * someone else's allocator, or when the calling thread cannot afford the device-wide stall
  * of an allocation.  No voda_ctx is needed: it runs on the CURRENT device, on `stream`
  * (a cudaStream_t, NULL = default stream), asynchronously.
- *   - Shapes whose per-round scratch, about min(max_jobs, max_total_gpu) * (ceil(max_total_gpu/8) * 32 + 4 * speedup_stride + 16)
- *     bytes, exceeds 32 MiB are refused with VODA_E_TOO_LARGE and a message in errbuf.
+ *   - Shapes whose per-round scratch, about J * (ceil(max_total_gpu/8) * 32 + 4 * speedup_stride + 16)
+ *     bytes with J = min(max_jobs, max_total_gpu), exceeds 32 MiB are refused with VODA_E_TOO_LARGE and a
+ *     message in errbuf.  With max_max_proc declared (<= 32) the first term counts J/4 rows, not J.
  *   - All calls on a GPU share the array (it keeps the previous call's bytes; nothing needs
  *     clearing: the backtrack only uses what the same round's forward pass wrote).  Calls that overlap on
  *     the GPU race on it: serialise them.

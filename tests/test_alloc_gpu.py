@@ -220,6 +220,84 @@ def test_declared_bounds_are_enforced(ctx):
     assert (s == 8).all() and (g == 0).all()
 
 
+def _ffdl_dev(c, b, declared):
+    """voda_allocate_dev on a device copy of b with max_max_proc = declared (0: not declared)."""
+    import torch
+    dev = torch.device("cuda", 0)
+    db = b.to_device(dev)
+    db.max_max_proc = declared
+    g = torch.full((max(1, b.jobs),), -7, dtype=torch.int32, device=dev)
+    s = torch.full((b.rounds,), -1, dtype=torch.int32, device=dev)
+    c.allocate_dev(db, g, s)
+    c.sync()
+    return g.cpu().numpy()[:b.jobs], s.cpu().numpy()
+
+
+@pytest.mark.parametrize("jobs", [1, 4, 5, 8, 9, 61, 256])
+def test_ffdl_declared_max_max_proc(ctx, oracle, jobs):
+    """The device entry point with the bound on the GPUs one job can take declared (scratch holds
+    the checkpoint rows only), not declared, and declared above 32 (every row stored): one answer."""
+    b = synth.jobs_batch("FfDLOptimizer", rounds=40, jobs_per_round=jobs, total_gpu=300, ragged=True)
+    b.total_gpu[:] = np.resize(np.array([0, 1, 7, 64, 300, 299, 33, 150], np.int32), b.rounds)
+    g_ref, s_ref = oracle.allocate(b, dense=True, threads=8)
+    top = int(b.max_proc.max())
+    assert top <= 32
+    for declared in (0, top, 32, 33, 1000):
+        g, s = _ffdl_dev(ctx, b, declared)
+        assert np.array_equal(s, s_ref), declared
+        assert np.array_equal(g, g_ref), declared
+
+
+def test_ffdl_declared_max_max_proc_is_enforced(ctx, oracle):
+    """A round in which a job can take more GPUs than declared reports VODA_ST_BOUND (its jobs get
+    0); min(MaxNumProc, total_gpu) is what counts, and the other rounds are unaffected."""
+    b = synth.jobs_batch("FfDLOptimizer", rounds=30, jobs_per_round=20, total_gpu=200, ragged=False)
+    b.max_proc = np.minimum(b.max_proc, 8).astype(np.int32)
+    first = b.job_off[:-1]
+    for r, m in ((3, 9), (11, 33), (12, 40), (20, 9), (29, 1 << 20)):
+        b.max_proc[first[r] + 2] = m
+    b.total_gpu[5] = 6   # no job can take more than 6 here
+    b.max_proc[first[5] + 1] = 50  # ... whatever MaxNumProc says
+    b.total_gpu[3] = 8   # and round 3 is inside a bound of 8 after all
+    g_ref, s_ref = oracle.allocate(b, dense=True, threads=8)
+    for declared in (8, 32):
+        g, s = _ffdl_dev(ctx, b, declared)
+        # which rounds break the bound: some job with min(max_proc, total) > declared
+        top = np.array([min(int(b.max_proc[b.job_off[r]:b.job_off[r + 1]].max()), int(b.total_gpu[r]))
+                        for r in range(b.rounds)])
+        over = top > declared
+        assert np.nonzero(over)[0].tolist() == ([11, 12, 20, 29] if declared == 8 else [11, 12, 29])
+        assert (s[over] == 8).all()
+        assert np.array_equal(s[~over], s_ref[~over])
+        per_round = np.repeat(over, np.diff(b.job_off))
+        assert (g[per_round] == 0).all()
+        assert np.array_equal(g[~per_round], g_ref[~per_round])
+
+
+def test_ffdl_declared_bound_shrinks_the_scratch(oracle):
+    """What the declaration buys: a context that ran a declared batch holds about a quarter of
+    the device memory of one that ran the same batch undeclared."""
+    import torch
+    from vodascheduler_b200 import Context
+    b = synth.jobs_batch("FfDLOptimizer", rounds=1500, jobs_per_round=256, total_gpu=1024, ragged=False)
+    used = {}
+    for declared in (0, 32):  # torch's own (cached) tensors are counted in the first, larger, figure
+        torch.cuda.synchronize()
+        c = Context(0)
+        try:
+            free0 = torch.cuda.mem_get_info(0)[0]
+            g, s = _ffdl_dev(c, b, declared)
+            used[declared] = free0 - torch.cuda.mem_get_info(0)[0]
+            if not declared:
+                first = (g.copy(), s.copy())
+            else:
+                assert np.array_equal(g, first[0]) and np.array_equal(s, first[1])
+        finally:
+            c.close()
+    assert used[0] > (1 << 30)
+    assert used[32] < 0.35 * used[0], used
+
+
 def test_ffdl_packed_rows_opt_in(oracle, monkeypatch):
     """VODA_PACK_ROWS=1: the host path ships only the speedup entries FfDL can read (packed
     rows + offsets); results must not change."""

@@ -72,7 +72,8 @@ def test_static_scratch_rejects_oversize_shape():
         torch.cuda.set_device(0)
         b = synth.jobs_batch("FfDLOptimizer", rounds=2, jobs_per_round=8, total_gpu=16)
         db = b.to_device(torch.device("cuda", 0))
-        db.max_jobs, db.max_total_gpu = 4096, 8192  # 4096 * 2048 * 8 B = 64 MiB per round
+        db.max_jobs, db.max_total_gpu = 2048, 8192  # 2048 rows * 1024 tiles * 32 B = 64 MiB per round
+        db.max_max_proc = 0
         out = torch.zeros(b.jobs, dtype=torch.int32, device="cuda")
         st = torch.zeros(b.rounds, dtype=torch.int32, device="cuda")
         err = C.create_string_buffer(256)
@@ -80,5 +81,14 @@ def test_static_scratch_rejects_oversize_shape():
         rc = ctx._lib.voda_ffdl_allocate_static(None, C.byref(s), out.data_ptr(), st.data_ptr(), err, len(err))
         assert rc == _abi.E_TOO_LARGE
         assert b"exceeds the static scratch" in err.value
+        # with the bound on the GPUs one job can take declared only every 4th row is kept: 16 MiB, it fits
+        db.max_max_proc = int(b.max_proc.max())
+        assert db.max_max_proc <= 32
+        s = db.struct()
+        rc = ctx._lib.voda_ffdl_allocate_static(None, C.byref(s), out.data_ptr(), st.data_ptr(), err, len(err))
+        assert rc == 0, err.value
+        torch.cuda.synchronize()
+        g_ref, s_ref = ctx.allocate(b)
+        assert np.array_equal(out.cpu().numpy(), g_ref) and np.array_equal(st.cpu().numpy(), s_ref)
     finally:
         ctx.close()

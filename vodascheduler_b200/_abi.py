@@ -34,6 +34,7 @@ class AllocBatchStruct(C.Structure):
         ("compaction_threshold", C.c_int32), ("max_jobs", C.c_int32),
         ("max_total_gpu", C.c_int32),
         ("speedup_off", C.c_void_p), ("speedup_len", C.c_int64),
+        ("max_max_proc", C.c_int32), ("reserved0", C.c_int32),
     ]
 
 

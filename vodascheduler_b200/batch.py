@@ -44,7 +44,8 @@ class AllocBatch:
     def __init__(self, algo, job_off, total_gpu, *, submit_sec=None, submit_nsec=None,
                  first_sec=None, first_nsec=None, priority=None, num_proc=None, min_proc=None,
                  max_proc=None, remaining_sec=None, speedup=None, speedup_stride=0,
-                 queue_num=0, compaction_threshold=-1, max_jobs=0, max_total_gpu=0, speedup_off=None):
+                 queue_num=0, compaction_threshold=-1, max_jobs=0, max_total_gpu=0, speedup_off=None,
+                 max_max_proc=0):
         if isinstance(algo, str):
             algo = _abi.ALGO_NAMES.index(algo)
         self.algo = int(algo)
@@ -63,6 +64,7 @@ class AllocBatch:
         self.compaction_threshold = int(compaction_threshold)
         self.max_jobs = int(max_jobs)
         self.max_total_gpu = int(max_total_gpu)
+        self.max_max_proc = int(max_max_proc)  # declared bound of the GPUs one job can take; 0: not declared
 
     @property
     def rounds(self):
@@ -85,6 +87,7 @@ class AllocBatch:
         s.compaction_threshold = self.compaction_threshold
         s.max_jobs = self.max_jobs
         s.max_total_gpu = self.max_total_gpu
+        s.max_max_proc = getattr(self, "max_max_proc", 0)
         return s
 
     def with_algo(self, algo):
@@ -112,7 +115,8 @@ class AllocBatch:
         return AllocBatch(self.algo, self.job_off[r0:r1 + 1] - j0, self.total_gpu[r0:r1],
                           speedup_stride=self.speedup_stride, queue_num=self.queue_num,
                           compaction_threshold=self.compaction_threshold,
-                          max_jobs=self.max_jobs, max_total_gpu=self.max_total_gpu, **kw)
+                          max_jobs=self.max_jobs, max_total_gpu=self.max_total_gpu,
+                          max_max_proc=getattr(self, "max_max_proc", 0), **kw)
 
     def bounds(self):
         n = np.diff(self.job_off)
@@ -128,6 +132,8 @@ class AllocBatch:
         mj, mt = self.bounds()
         b.max_jobs = self.max_jobs or mj
         b.max_total_gpu = self.max_total_gpu or mt
+        if not getattr(self, "max_max_proc", 0) and self.max_proc is not None and self.max_proc.size:
+            b.max_max_proc = max(1, int(self.max_proc.max()))  # declared like the two bounds above
         for name, _ in _ALLOC_ARRAYS:
             v = getattr(self, name)
             setattr(b, name, None if v is None else torch.from_numpy(v).to(device))

@@ -189,6 +189,7 @@ AllocArgs make_args(const voda_alloc_batch* b) {
   a.compaction = b->compaction_threshold >= 0 ? b->compaction_threshold : 10;  // elastic_tiresias.go:21
   a.max_jobs = b->max_jobs;
   a.max_total = b->max_total_gpu;
+  a.max_gmax = b->max_max_proc > 0 ? b->max_max_proc : 0;
   return a;
 }
 
@@ -598,6 +599,10 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     a.job_base = j0;
     a.max_jobs = max_jobs;
     a.max_total = max_total;
+    // FfDL keeps a quarter of its DP rows when no job of the chunk can take more than 32 GPUs: the
+    // host arrays are here, so the bound is the chunk's own
+    if (b->algo == VODA_ALGO_FFDL_OPTIMIZER && a.max_gmax == 0 && nj > 0)
+      a.max_gmax = std::max(1, max_i32(b->max_proc, j0, j1));
     a.job_off = (const int32_t*)(base + o_off);
     a.total_gpu = (const int32_t*)(base + o_tot);
     a.submit_sec = (f & F_SUBMIT) ? (const int64_t*)(base + o_ss) : nullptr;

@@ -38,6 +38,7 @@ struct AllocArgs {
   int32_t compaction;  // ElasticTiresiasCompactionThreshold
   int32_t max_jobs;    // declared upper bound of jobs per round
   int32_t max_total;   // declared upper bound of total_gpu
+  int32_t max_gmax;    // declared upper bound of min(MaxNumProc, total_gpu) over the batch; 0: not declared
   int32_t* out_gpus;
   int32_t* out_status;
 };

@@ -106,11 +106,14 @@ struct FfdlScratch {
   FfdlMeta* meta;     // [count]
   FfdlRow* rows;      // [count][Jcap]
   float* srows;       // [count][Jcap][SW]  S rows in sorted order, -inf beyond the table limit
-  float* P;           // [count][Jcap][rowFloats]  P[j][1..K]: row j-1, float k-1
+  float* P;           // [count][slabRows][rowFloats].  A round that stores every row keeps P[j][1..K]
+                      // in slab row j-1 (float k-1); a sparse round keeps P[c], c a multiple of kCkpt,
+                      // in slab row c/kCkpt - 1: its stored rows lie together
   size_t rowFloats;   // 8 * KTcap
-  size_t slabFloats;  // Jcap * rowFloats
+  size_t slabFloats;  // slabRows * rowFloats
   int Jcap;
   int SW;
+  int sparseOnly;     // the slab holds checkpoint rows only (the declared max_max_proc makes every round sparse)
 };
 
 // A DP row in shared memory.  Group q holds P[4q-3 .. 4q] (group 0 = three cells left of the
@@ -228,7 +231,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // Everything the row loop and the backtrack need to know about the rows of one round, worked
 // out once after the sort: the sorted S rows (to scratch), the row maxima, the two running
 // sums behind the trims, the tile ranges.
-__device__ bool ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, int K, int KT, int SW,
+__device__ int ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, int J, int K, int KT, int SW,
                                 float* gs, FfdlRow* grows) {
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int W = a.stride;
@@ -307,7 +310,7 @@ __device__ bool ffdl_setup_rows(const AllocArgs& a, const FfdlSmem& sm, int o, i
     grows[j].klim = klim;
   }
   __syncthreads();
-  return __reduce_max_sync(0xffffffffu, gtop) <= kCkptGmax;  // kThreads == 32
+  return __reduce_max_sync(0xffffffffu, gtop);  // kThreads == 32; the most GPUs any job of the round can take
 }
 
 // All DP rows of one round.  Returns with the last row in `*last` (shared memory).
@@ -345,10 +348,10 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT,
   const int sB = SW >= 8 ? 1 : 0;  // SW >= 4: the second block is clamped
   const int gslow0 = max(a.stride, 1);
   float cprev = 0.0f;  // c_0: P[0][k] = 0
-  float4* grow = reinterpret_cast<float4*>(slab);  // row j of P goes to slab row j-1
+  float4* const slab4 = reinterpret_cast<float4*>(slab);
   const size_t rowGroups = rowFloats / 4;
   FfdlRow* gr = grows;
-  for (int j = 1; j <= J; j++, grow += rowGroups, gr++) {
+  for (int j = 1; j <= J; j++, gr++) {
     const unsigned long long rq = rowq[j - 1];
     stage_s();  // row j+1; its slot was last read two barriers ago
     const float4* s4 = sm.sring + ((j - 1) & 3) * sGroups;
@@ -361,7 +364,9 @@ __device__ void ffdl_rows(const AllocArgs& a, const FfdlSmem& sm, int J, int KT,
     const float ccur = fmaxf(-10000.0f, srmax[j - 1] + cprev);
     if (tid == 0) gr->c = ccur;
     // row J is only read at [K], from shared memory; a sparse round stores every kCkpt-th row
-    float4* gdst = (j < J && (!sparse || j % kCkpt == 0)) ? grow : nullptr;
+    // (slab row j-1, or j/kCkpt - 1 among the checkpoint rows)
+    float4* gdst = (j < J && (!sparse || j % kCkpt == 0)) ? slab4 + (size_t)(sparse ? j / kCkpt - 1 : j - 1) * rowGroups
+                                                          : nullptr;
     // passes of 32 tiles from the right end of the band; lanes beyond the band recompute its last
     // tile and store nothing (every lane must reach the __syncwarp in front of the stores)
     {
@@ -462,7 +467,13 @@ __global__ void __launch_bounds__(kThreads, VODA_FFDL_MINBLOCKS)
     const int KT = (K + kCells - 1) / kCells;
     float* gs = sc.srows + (size_t)rr * (size_t)sc.Jcap * (size_t)SW;
     FfdlRow* grows = sc.rows + (size_t)rr * (size_t)sc.Jcap;
-    const bool sparse = ffdl_setup_rows(a, sm, o, J, K, KT, SW, gs, grows);
+    const int gtop = ffdl_setup_rows(a, sm, o, J, K, KT, SW, gs, grows);
+    const bool sparse = gtop <= kCkptGmax;
+    if (a.max_gmax > 0 && gtop > a.max_gmax) {  // some job can take more GPUs than the caller declared (max_max_proc)
+      meta.st = VODA_ST_BOUND;
+      if (tid == 0) sc.meta[rr] = meta;
+      continue;
+    }
     const float4* last = nullptr;
     ffdl_rows(a, sm, J, KT, SW, ost, sparse, sc.P + (size_t)rr * sc.slabFloats, sc.rowFloats, gs, grows, &last);
     const float PJK = cell(last, ost, K);
@@ -529,7 +540,7 @@ __device__ __forceinline__ int ffdl_segment(const float* slab, const float* gsro
     if (lane >= 1 && lane <= kCkpt) prefetch_l2(gsrows + (c - kCkpt + lane - 1) * SW);
     // ... and so is the stretch of the next checkpoint row just below the current position
     if (lane >= 8 && lane < 12 && c > kCkpt)
-      prefetch_l2(slab + (c - kCkpt - 1) * rowFloats + max(k - 1 - 32 * (lane - 8), 0));
+      prefetch_l2(slab + (c / kCkpt - 2) * rowFloats + max(k - 1 - 32 * (lane - 8), 0));
   }
 #pragma unroll
   for (int i = 0; i < NR; i++) {
@@ -550,7 +561,7 @@ __device__ __forceinline__ int ffdl_segment(const float* slab, const float* gsro
   const int width = k - base;  // <= kBand: columns base .. k-1
   // 1. the stored row c (or row 0 = 0)
   {
-    const float* crow = slab + max(c - 1, 0) * rowFloats;  // P[c][x] at crow[x-1]
+    const float* crow = slab + max(c / kCkpt - 1, 0) * rowFloats;  // P[c][x] at crow[x-1]
     const float cC = __int_as_float(recc.w);
     for (int idx = lane; idx < width; idx += 32) {
       const int x = base + idx;
@@ -760,6 +771,14 @@ static size_t ffdl_jcap(const AllocArgs& a) {
   return (size_t)(j > 0 ? j : 1);
 }
 
+// Rows of P a round's slab holds.  When the caller declared that no job can take more than
+// kCkptGmax GPUs every round is a sparse one: only the checkpoint rows exist.
+static bool ffdl_sparse_only(const AllocArgs& a) { return a.max_gmax > 0 && a.max_gmax <= kCkptGmax; }
+static size_t ffdl_slab_rows(const AllocArgs& a) {
+  const size_t Jcap = ffdl_jcap(a);
+  return ffdl_sparse_only(a) ? (Jcap - 1) / kCkpt + 1 : Jcap;
+}
+
 // Scratch one round needs: its P slab, the sorted S rows, the row records and the meta record
 // (every part a multiple of 16 bytes).
 size_t ffdl_scratch_per_round(const AllocArgs& a) {
@@ -767,7 +786,7 @@ size_t ffdl_scratch_per_round(const AllocArgs& a) {
   size_t smem;
   ffdl_shape(a, &KTcap, &SW, &Jp, &smem);
   const size_t Jcap = ffdl_jcap(a);
-  return Jcap * (size_t)KTcap * 32 + Jcap * (size_t)SW * 4 + Jcap * sizeof(FfdlRow) + sizeof(FfdlMeta);
+  return ffdl_slab_rows(a) * (size_t)KTcap * 32 + Jcap * (size_t)SW * 4 + Jcap * sizeof(FfdlRow) + sizeof(FfdlMeta);
 }
 
 size_t ffdl_smem_bytes(const AllocArgs& a) {
@@ -791,7 +810,8 @@ cudaError_t launch_ffdl(const AllocArgs& a, int r0, int count, int sms, void* sc
   FfdlScratch sc;
   unsigned char* base = static_cast<unsigned char*>(scratch);
   sc.rowFloats = (size_t)KTcap * 8;
-  sc.slabFloats = Jcap * sc.rowFloats;
+  sc.slabFloats = ffdl_slab_rows(a) * sc.rowFloats;
+  sc.sparseOnly = ffdl_sparse_only(a) ? 1 : 0;
   sc.Jcap = (int)Jcap;
   sc.SW = SW;
   size_t off = 0;

@@ -108,6 +108,7 @@ extern "C" int voda_ffdl_allocate_static(void* stream, const voda_alloc_batch* b
   a.compaction = 10;
   a.max_jobs = b->max_jobs;
   a.max_total = b->max_total_gpu;
+  a.max_gmax = b->max_max_proc > 0 ? b->max_max_proc : 0;
   a.out_gpus = d_out_gpus;
   a.out_status = d_out_status;
 
