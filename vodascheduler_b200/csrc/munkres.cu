@@ -6,7 +6,7 @@
 // C is only read again by step 6 (a handful of times per matrix), so it lives in a per-CTA
 // slab of global scratch that stays L2-resident (16 KB per matrix as uint8), NOT in shared
 // memory: the solve is a chain of dependent warp steps, throughput comes from how many
-// matrices an SM works on at once, and with ~1.3 KB of shared memory per matrix that is the
+// matrices an SM works on at once, and with ~5 KB of shared memory per matrix that is the
 // hardware limit of 32 one-warp CTAs per SM.  The cell type is found by trying: the uint8
 // kernel runs over the whole batch and marks the matrices whose range does not fit; the
 // uint16 / int32 / int64 kernels then pick up only what was marked (each is an almost-empty
@@ -48,9 +48,9 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
   sm.ra = smem_raw + off; off += 128 * sizeof(Pot);
   sm.starCol = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
   sm.starRow = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
-  sm.primeCol = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
+  sm.primeCol = smem_raw + off; off += 128 * sizeof(short);
   sm.zt = reinterpret_cast<uint32_t*>(smem_raw + off); off += 128 * 4 * sizeof(uint32_t);
-  sm.ccs = reinterpret_cast<uint32_t*>(smem_raw + off);
+  sm.zr = reinterpret_cast<uint32_t*>(smem_raw + off);
   const int lane = threadIdx.x;
   const unsigned full = 0xffffffffu;
   const long long NEG = (long long)0x8000000000000000ULL;
@@ -58,13 +58,11 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
   for (int b = blockIdx.x; b < batch; b += gridDim.x) {
     if (need[b] != level) continue;
     const int64_t* M = A + (size_t)b * n * n;
-    uint32_t Z[4][4];
-#pragma unroll
-    for (int q = 0; q < 4; q++)
-#pragma unroll
-      for (int t = 0; t < 4; t++) Z[q][t] = 0;
     bool overflow = false;
-    for (int x = lane; x < 128 * 4; x += 32) sm.zt[x] = 0;
+    for (int x = lane; x < 128 * 4; x += 32) {
+      sm.zt[x] = 0;
+      sm.zr[x] = 0;
+    }
     __syncwarp();
     for (int l = 0; l < 32 && 4 * l < n; l++) {
       // 4 rows x 4 column blocks in flight
@@ -109,7 +107,7 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
           if (c > (unsigned long long)CellMax<CellT>::v) overflow = true;
           if (valid) C[(size_t)i * n + col] = (CellT)c;
           const unsigned bz = __ballot_sync(full, valid && c == 0);
-          if (lane == l) Z[q][t] = bz;
+          if (lane == 0) sm.zr[i * 4 + t] = bz;
           if (valid && c == 0) sm.zt[col * 4 + (i >> 5)] |= 1u << (i & 31);  // this lane owns column col
         }
       }
@@ -124,7 +122,7 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
       continue;
     }
     __syncwarp();
-    munkres_solve<CellT>(C, n, Z, sm);
+    munkres_solve<CellT>(C, n, sm);
     for (int i = lane; i < n; i += 32) out[(size_t)b * n + i] = sm.starCol[i];
     if (lane == 0) status[b] = VODA_ST_OK;
     __syncwarp();
@@ -134,7 +132,7 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
 template <typename CellT>
 size_t munkres_smem() {
   using Pot = typename MunkresTypes<CellT>::Pot;
-  return 128 * sizeof(Pot) + 3 * 128 * sizeof(short) + 128 * 4 * sizeof(uint32_t) + 4 * sizeof(uint32_t) + 16;
+  return 128 * sizeof(Pot) + 3 * 128 * sizeof(short) + 2 * 128 * 4 * sizeof(uint32_t) + 16;
 }
 
 constexpr int kCtasPerSm = 32;  // one-warp CTAs: the hardware limit of resident CTAs per SM

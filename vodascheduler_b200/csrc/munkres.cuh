@@ -11,13 +11,16 @@
 //     in shared memory in the narrowest cell type that holds it;
 //   * step 6 (add m to covered rows, subtract m from uncovered columns) only moves row / column
 //     potentials: value(i,j) = C[i][j] + ra[i] - cs[j];
-//   * each lane owns 4 consecutive rows and keeps their 128-bit ZERO MASKS in registers, so
-//     "first uncovered zero in row-major order" (step 4, ~n^2/16 times per matrix) is one
-//     ballot + two find-first-set instead of an n^2 scan; step 6 patches the masks (covered
-//     rows lose their zeros in covered columns; uncovered x uncovered cells equal to m gain one);
-//   * stars / primes are starCol[row], starRow[col], primeCol[row] in shared memory, and so
-//     are the column covers and a column-major copy of the zero masks (which rows have a zero
-//     in column j), so that a step-4 iteration is ~40 instructions.
+//   * every row has a 128-bit ZERO MASK (shared memory, row-major and column-major copies), so
+//     "first uncovered zero in row-major order" (step 4, ~n^2/16 times per matrix) never scans
+//     the matrix; step 6 patches the masks (covered rows lose their zeros in covered columns;
+//     uncovered x uncovered cells equal to m gain one); each lane owns 4 consecutive rows;
+//   * stars / primes are starCol[row], starRow[col], primeCol[row] in shared memory, and so is
+//     a column-major copy of the zero masks (which rows have a zero in column j); every owned
+//     row carries a key (row, first uncovered zero column, column of its star), so a step-4
+//     iteration is one redux over the keys, one shared-memory load and a dozen ALU operations;
+//   * with 32-bit potentials step 6 takes the minimum row by row (a redux each) and then looks
+//     for new zeros only in the rows whose minimum is the global one.
 #pragma once
 
 #include "common.cuh"
@@ -38,13 +41,13 @@ struct MunkresTypes<int64_t> {
 };
 
 struct MunkresSmem {
-  short* starCol;   // [128] column of the star in row i, -1 if none
+  short* starCol;   // [128] column of the star in row i, -1 if none (8-byte aligned)
   short* starRow;   // [128] row of the star in column j, -1 if none
-  short* primeCol;  // [128] column of the prime in row i (valid for rows covered in this phase)
+  unsigned char* primeCol;  // [128] column of the prime in row i (valid for rows covered in this phase)
   void* ra;         // [128] row potentials (Pot)
+  uint32_t* zr;     // [128][4] row-major zero masks: bit j of zr[i] = (value(i, j) == 0) (16-byte aligned)
   uint32_t* zt;     // [128][4] column-major zero masks: bit i of zt[j] = (value(i, j) == 0);
-                    //          the caller fills it together with the row-major masks Z
-  uint32_t* ccs;    // [4] column covers
+                    //          the caller fills both (rows and columns beyond n: no bits)
 };
 
 __device__ __forceinline__ void mask_set(uint32_t (&m)[4], int idx) {
@@ -84,11 +87,10 @@ __device__ __forceinline__ T warp_min(T v) {
   return v;
 }
 
-// Solve.  C: n*n cells (row stride n) already holding rowmax_i - A[i][j]; Z: the zero masks of
-// the calling lane's rows (bit j of Z[q] = C[4*lane+q][j] == 0).  On return sm.starCol[i] is
-// the column assigned to row i.  Must be called by one full warp.
+// Solve.  C: n*n cells (row stride n) already holding rowmax_i - A[i][j]; sm.zr / sm.zt: its zero
+// masks.  On return sm.starCol[i] is the column assigned to row i.  Must be called by one full warp.
 template <typename CellT>
-__device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[4][4], const MunkresSmem& sm) {
+__device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresSmem& sm) {
   using Pot = typename MunkresTypes<CellT>::Pot;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
@@ -98,96 +100,113 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
     ra[i] = 0;
     sm.starCol[i] = -1;
     sm.starRow[i] = -1;
-    sm.primeCol[i] = -1;
+    sm.primeCol[i] = 0;
   }
   __syncwarp();
 
   // ---- step 2: star the first zero of each row whose column holds no star yet, rows in order
+  uint4* zr4 = reinterpret_cast<uint4*>(sm.zr);
   uint32_t starred[4] = {0, 0, 0, 0};  // columns holding a star (uniform)
   int nstar = 0;
-  for (int l = 0; l < 32 && 4 * l < n; l++) {
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-      const int i = 4 * l + q;
-      if (i >= n) break;
-      int col = -1;
-#pragma unroll
-      for (int t = 3; t >= 0; t--) {
-        const uint32_t cand = Z[q][t] & ~starred[t];
-        if (cand) col = 32 * t + __ffs(cand) - 1;
-      }
-      col = __shfl_sync(full, col, l);
-      if (col >= 0) {
-        mask_set(starred, col);
-        nstar++;
-        if (lane == 0) {
-          sm.starCol[i] = (short)col;
-          sm.starRow[col] = (short)i;
-        }
+  for (int i = 0; i < n; i++) {
+    const uint4 z = zr4[i];  // the same address in every lane
+    const uint32_t c0 = z.x & ~starred[0], c1 = z.y & ~starred[1], c2 = z.z & ~starred[2], c3 = z.w & ~starred[3];
+    int col = -1;
+    if (c3) col = 96 + __ffs(c3) - 1;
+    if (c2) col = 64 + __ffs(c2) - 1;
+    if (c1) col = 32 + __ffs(c1) - 1;
+    if (c0) col = __ffs(c0) - 1;
+    if (col >= 0) {
+      mask_set(starred, col);
+      nstar++;
+      if (lane == 0) {
+        sm.starCol[i] = (short)col;
+        sm.starRow[col] = (short)i;
       }
     }
   }
   __syncwarp();
 
-  // Covers.  Columns: 128 bits in shared memory (sm.ccs), copied to registers when a whole
-  // mask is needed.  Rows: each lane keeps the state of the 4 rows it owns.
+  // Covers.  Rows: each lane keeps the state of the 4 rows it owns (in RB, below).  Columns: inside one
+  // step-4 phase the covered columns are the starred ones minus the star columns of the rows
+  // covered so far, so nothing is stored per iteration; step 6 rebuilds the mask when it needs it.
   //
-  // k[q] = (q << 8) | first uncovered zero column of owned row q, or kBig when the row is
-  // covered or has none.  Inside one step-4 phase columns only get UNcovered and rows only get
-  // covered, so uncovering column sc turns k[q] into min(k[q], (q << 8) | sc) for the live rows
-  // that have a zero there — read from the column-major zero masks sm.zt — and the search
-  // "first uncovered zero in row-major order" never rescans anything: it is the minimum key
-  // of the lowest lane that has one.
-  constexpr int kBig = 0x7fffffff;
+  // K[q] = (row << 16) | (first uncovered zero column of owned row q << 8) | (column of the row's
+  // star, 0xFF if it has none), or a value >= kDead when the row is covered or has no uncovered zero.
+  // RB[q] is the key of owned row q without its column; covering the row sets kCovered in it (the
+  // star's column stays readable in the low 7 bits), so that whatever is merged into K[q]
+  // afterwards stays >= kDead: no separate "row is live" test in the loop.  Inside
+  // a phase columns only get UNcovered and rows only get covered, so uncovering column sc turns
+  // K[q] into min(K[q], key with column sc) for the live rows that have a zero there — read from
+  // the column-major zero masks sm.zt — and the search "first uncovered zero in row-major order"
+  // never rescans anything: it is the minimum key of the warp (one redux), which carries the row,
+  // the column and the row's star.
+  constexpr int kNone = 0x7fffffff;
+  constexpr int kDead = 0x7fff0000;     // keys from here up are no candidates (and have bit 7 set)
+  constexpr int kCovered = 0x7fff0080;  // OR-ed into RB[q] and K[q] when the row gets covered
   uint32_t colCov[4] = {starred[0], starred[1], starred[2], starred[3]};  // step 3
   bool ucolValid[4];
 #pragma unroll
   for (int t = 0; t < 4; t++) ucolValid[t] = lane + 32 * t < n;
-  int k[4];
-  uint32_t live = 0xFu;  // owned rows not covered
-  auto reset_phase = [&]() {  // covers = {starred columns}, no row; keys from the zero masks
-    if (lane < 4) sm.ccs[lane] = lane == 0 ? colCov[0] : lane == 1 ? colCov[1] : lane == 2 ? colCov[2] : colCov[3];
-    live = 0xFu;
+  int K[4], RB[4];
+  auto keys_from_masks = [&]() {
 #pragma unroll
     for (int q = 0; q < 4; q++) {
-      k[q] = kBig;
-#pragma unroll
-      for (int t = 3; t >= 0; t--) {
-        const uint32_t cand = Z[q][t] & ~colCov[t];
-        if (cand) k[q] = (q << 8) | (32 * t + __ffs(cand) - 1);
+      K[q] = kNone;
+      if (RB[q] < kDead) {
+        const uint4 z = zr4[4 * lane + q];
+        const uint32_t c0 = z.x & ~colCov[0], c1 = z.y & ~colCov[1], c2 = z.z & ~colCov[2], c3 = z.w & ~colCov[3];
+        if (c3) K[q] = RB[q] | ((96 + __ffs(c3) - 1) << 8);
+        if (c2) K[q] = RB[q] | ((64 + __ffs(c2) - 1) << 8);
+        if (c1) K[q] = RB[q] | ((32 + __ffs(c1) - 1) << 8);
+        if (c0) K[q] = RB[q] | ((__ffs(c0) - 1) << 8);
       }
     }
-    __syncwarp();
+  };
+  auto reset_phase = [&]() {  // covers = {starred columns}, no row; keys from the zero masks
+    const short4 sc4 = *reinterpret_cast<const short4*>(sm.starCol + 4 * lane);
+    RB[0] = ((4 * lane + 0) << 16) | (sc4.x & 0xFF);
+    RB[1] = ((4 * lane + 1) << 16) | (sc4.y & 0xFF);
+    RB[2] = ((4 * lane + 2) << 16) | (sc4.z & 0xFF);
+    RB[3] = ((4 * lane + 3) << 16) | (sc4.w & 0xFF);
+    keys_from_masks();
   };
   reset_phase();
-  const int ztWord = lane >> 3, ztShift = 4 * (lane & 7);
+  // shared-memory addresses and shifts of the step-4 loop, made opaque so that they stay in
+  // registers (recomputing them costs a fifth of an iteration)
+  uint32_t ztAddr = (uint32_t)__cvta_generic_to_shared(sm.zt) + 4u * (uint32_t)(lane >> 3);
+  uint32_t primeAddr = (uint32_t)__cvta_generic_to_shared(sm.primeCol);
+  uint32_t ztShift = 4u * (uint32_t)(lane & 7);
+  asm volatile("" : "+r"(ztAddr), "+r"(primeAddr), "+r"(ztShift));
 
   while (nstar < n) {
     // ---- step 4: first uncovered zero in row-major order
-    const int key = min(min(k[0], k[1]), min(k[2], k[3]));
-    const unsigned b = __ballot_sync(full, key != kBig);
-    if (b) {
-      const int ls = __ffs(b) - 1;
-      const int packed = __shfl_sync(full, key, ls);
-      const int row = 4 * ls + (packed >> 8), col = packed & 255;
-      const int sc = sm.starCol[row];
-      if (sc >= 0) {  // prime it, cover its row, uncover the star's column
-        if (lane == 0) {
-          sm.primeCol[row] = (short)col;
-          sm.ccs[sc >> 5] &= ~(1u << (sc & 31));
-        }
-        if (lane == ls) {  // the chosen key is this lane's k[q] of the covered row
-          live &= ~(1u << (packed >> 8));
+    const int red = __reduce_min_sync(full, min(min(K[0], K[1]), min(K[2], K[3])));
+    if ((red & 0x80) == 0) {  // it lies in a row that holds a star: prime it, cover its row, uncover the star's column
+      const int sc = red & 0x7f;
+      const int row = red >> 16;
+      uint32_t word;
+      asm volatile("ld.shared.u32 %0, [%1];" : "=r"(word) : "r"(ztAddr + 16u * (uint32_t)sc));
+      // every lane stores the same value: no predicate to keep
+      asm volatile("st.shared.u8 [%0], %1;" ::"r"(primeAddr + (uint32_t)row), "r"(red >> 8) : "memory");
 #pragma unroll
-          for (int q = 0; q < 4; q++) k[q] = k[q] == packed ? kBig : k[q];
-        }
-        const uint32_t hits = (sm.zt[sc * 4 + ztWord] >> ztShift) & live;
+      for (int q = 0; q < 4; q++) {  // the chosen key is some lane's K[q] of the row that gets covered
+        const bool me = K[q] == red;
+        K[q] = me ? kNone : K[q];
+        RB[q] = me ? (RB[q] | kCovered) : RB[q];
+      }
+      const uint32_t hits = (word >> ztShift) & 0xFu;
+      if (hits) {  // zeros are sparse: most lanes, most of the time, have none in that column
+        const int cb = sc << 8;
 #pragma unroll
         for (int q = 0; q < 4; q++)
-          if ((hits >> q) & 1u) k[q] = min(k[q], (q << 8) | sc);
-        continue;
+          if ((hits >> q) & 1u) K[q] = min(K[q], RB[q] + cb);
       }
+      continue;
+    }
+    if (red < kDead) {
       // ---- step 5: augment along the alternating path that starts at the prime (row, col)
+      const int row = red >> 16, col = (red >> 8) & 0xFF;
       int last = col;
       if (lane == 0) {
         int r = row, c = col;
@@ -210,11 +229,18 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
       reset_phase();
       continue;
     }
-    // ---- step 6 needs whole masks: columns from shared memory, rows from the per-lane bits
+    // ---- step 6 needs whole masks.  Columns: the starred ones minus the star columns of the covered rows
     __syncwarp();
+    {
+      uint32_t unc[4] = {0, 0, 0, 0};
 #pragma unroll
-    for (int t = 0; t < 4; t++) colCov[t] = sm.ccs[t];
-    const uint32_t ownCov = ~live & 0xFu;
+      for (int q = 0; q < 4; q++)
+        if (RB[q] >= kDead) mask_set(unc, RB[q] & 0x7f);  // a covered row holds a star
+#pragma unroll
+      for (int t = 0; t < 4; t++) colCov[t] = starred[t] & ~__reduce_or_sync(full, unc[t]);
+    }
+    const uint32_t ownCov = (RB[0] >= kDead ? 1u : 0u) | (RB[1] >= kDead ? 2u : 0u) | (RB[2] >= kDead ? 4u : 0u) |
+                            (RB[3] >= kDead ? 8u : 0u);
     // rebuild the uniform row-cover mask from the per-lane bits (rows 4*lane .. 4*lane+3)
     uint32_t rowCov[4];
     {
@@ -228,19 +254,41 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
 #pragma unroll
     for (int t = 0; t < 4; t++) ucol[t] = ucolValid[t] && !((colCov[t] >> lane) & 1u);
     Pot mn = sizeof(Pot) == 8 ? (Pot)0x7fffffffffffffffLL : (Pot)0x7fffffff;
-    for (int i = 0; i < n; i++) {
-      if (mask_test(rowCov, i)) continue;
-      const Pot rai = ra[i];
-      const CellT* row = C + (size_t)i * n;
+    // 32-bit potentials: the minimum of every uncovered row is one redux, kept by lane l for rows
+    // l + 32 w, so that afterwards only the rows whose minimum IS m are searched for new zeros
+    int rmin[4] = {0x7fffffff, 0x7fffffff, 0x7fffffff, 0x7fffffff};
+    if constexpr (sizeof(Pot) == 4) {
+      for (int l = 0; l < 32 && l < n; l++) {
 #pragma unroll
-      for (int t = 0; t < 4; t++) {
-        if (ucol[t]) {
-          const Pot v = (Pot)row[lane + 32 * t] + rai - cs[t];
-          mn = v < mn ? v : mn;
+        for (int w = 0; w < 4; w++) {
+          const int i = 32 * w + l;
+          if (i >= n || ((rowCov[w] >> l) & 1u)) continue;
+          const int rai = (int)ra[i];
+          const CellT* row = C + (size_t)i * n;
+          int v = 0x7fffffff;
+#pragma unroll
+          for (int t = 0; t < 4; t++)
+            if (ucol[t]) v = min(v, (int)row[lane + 32 * t] + rai - (int)cs[t]);
+          const int rm = __reduce_min_sync(full, v);
+          if (lane == l) rmin[w] = rm;
         }
       }
+      mn = (Pot)__reduce_min_sync(full, min(min(rmin[0], rmin[1]), min(rmin[2], rmin[3])));
+    } else {
+      for (int i = 0; i < n; i++) {
+        if (mask_test(rowCov, i)) continue;
+        const Pot rai = ra[i];
+        const CellT* row = C + (size_t)i * n;
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+          if (ucol[t]) {
+            const Pot v = (Pot)row[lane + 32 * t] + rai - cs[t];
+            mn = v < mn ? v : mn;
+          }
+        }
+      }
+      mn = warp_min(mn);
     }
-    mn = warp_min(mn);
     for (int i = lane; i < n; i += 32)
       if (mask_test(rowCov, i)) ra[i] += mn;
 #pragma unroll
@@ -250,8 +298,12 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
 #pragma unroll
     for (int q = 0; q < 4; q++)
       if ((own >> q) & 1u) {
-#pragma unroll
-        for (int t = 0; t < 4; t++) Z[q][t] &= ~colCov[t];
+        uint4 z = zr4[4 * lane + q];
+        z.x &= ~colCov[0];
+        z.y &= ~colCov[1];
+        z.z &= ~colCov[2];
+        z.w &= ~colCov[3];
+        zr4[4 * lane + q] = z;
       }
 #pragma unroll
     for (int t = 0; t < 4; t++)
@@ -262,36 +314,47 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, uint32_t (&Z)[
       }
     __syncwarp();
     // uncovered x uncovered cells that were equal to m become zeros
-    for (int l = 0; l < 32 && 4 * l < n; l++) {
+    if constexpr (sizeof(Pot) == 4) {
 #pragma unroll
-      for (int q = 0; q < 4; q++) {
-        const int i = 4 * l + q;
-        if (i >= n) break;
-        if (mask_test(rowCov, i)) continue;
-        const Pot rai = ra[i];
-        const CellT* row = C + (size_t)i * n;
+      for (int w = 0; w < 4; w++) {
+        unsigned rows = __ballot_sync(full, rmin[w] == (int)mn);  // only these rows hold such a cell
+        while (rows) {
+          const int l = __ffs(rows) - 1;
+          rows &= rows - 1;
+          const int i = 32 * w + l;
+          const int rai = (int)ra[i];
+          const CellT* row = C + (size_t)i * n;
 #pragma unroll
-        for (int t = 0; t < 4; t++) {
-          const bool z = ucol[t] && ((Pot)row[lane + 32 * t] + rai - cs[t] == 0);
-          const unsigned bz = __ballot_sync(full, z);
-          if (lane == l) Z[q][t] |= bz;
-          if (z) sm.zt[(lane + 32 * t) * 4 + (i >> 5)] |= 1u << (i & 31);
+          for (int t = 0; t < 4; t++) {
+            const bool z = ucol[t] && ((int)row[lane + 32 * t] + rai - (int)cs[t] == 0);
+            const unsigned bz = __ballot_sync(full, z);
+            if (lane == 0 && bz) sm.zr[i * 4 + t] |= bz;
+            if (z) sm.zt[(lane + 32 * t) * 4 + w] |= 1u << l;
+          }
+        }
+      }
+    } else {
+      for (int l = 0; l < 32 && 4 * l < n; l++) {
+#pragma unroll
+        for (int q = 0; q < 4; q++) {
+          const int i = 4 * l + q;
+          if (i >= n) break;
+          if (mask_test(rowCov, i)) continue;
+          const Pot rai = ra[i];
+          const CellT* row = C + (size_t)i * n;
+#pragma unroll
+          for (int t = 0; t < 4; t++) {
+            const bool z = ucol[t] && ((Pot)row[lane + 32 * t] + rai - cs[t] == 0);
+            const unsigned bz = __ballot_sync(full, z);
+            if (lane == 0 && bz) sm.zr[i * 4 + t] |= bz;
+            if (z) sm.zt[(lane + 32 * t) * 4 + (i >> 5)] |= 1u << (i & 31);
+          }
         }
       }
     }
     __syncwarp();
     // the masks changed; the covers did not: rebuild the keys of the live rows
-#pragma unroll
-    for (int q = 0; q < 4; q++) {
-      k[q] = kBig;
-      if ((live >> q) & 1u) {
-#pragma unroll
-        for (int t = 3; t >= 0; t--) {
-          const uint32_t cand = Z[q][t] & ~colCov[t];
-          if (cand) k[q] = (q << 8) | (32 * t + __ffs(cand) - 1);
-        }
-      }
-    }
+    keys_from_masks();
   }
   __syncwarp();
 }

@@ -46,6 +46,11 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
   {
     unsigned char* p = smem_raw;
     sm.M = slabs + (size_t)blockIdx.x * slabInts;
+    sm.mk.zr = reinterpret_cast<uint32_t*>(p); p += 4 * 4 * 128;  // read as uint4: 16-byte aligned, so first
+    sm.mk.zt = reinterpret_cast<uint32_t*>(p); p += 4 * 4 * 128;
+    sm.mk.starCol = reinterpret_cast<short*>(p); p += 2 * 128;    // read as short4
+    sm.mk.starRow = reinterpret_cast<short*>(p); p += 2 * 128;
+    sm.mk.primeCol = p; p += 2 * 128;
     sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Mp;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
     sm.mk.ra = p; p += 8 * 128;
@@ -58,11 +63,6 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
     sm.eW = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
     sm.eNext = reinterpret_cast<int*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
     sm.rowmax = reinterpret_cast<int32_t*>(p); p += 4 * 128;
-    sm.mk.starCol = reinterpret_cast<short*>(p); p += 2 * 128;
-    sm.mk.starRow = reinterpret_cast<short*>(p); p += 2 * 128;
-    sm.mk.primeCol = reinterpret_cast<short*>(p); p += 2 * 128;
-    sm.mk.zt = reinterpret_cast<uint32_t*>(p); p += 4 * 4 * 128;
-    sm.mk.ccs = reinterpret_cast<uint32_t*>(p);
   }
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned full = 0xffffffffu;
@@ -247,12 +247,10 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
     __syncthreads();
     // ---- ComputeMunkresMax on M (warp 0), then rename + total score ------------------------
     if (warp == 0) {
-      uint32_t Z[4][4];
-#pragma unroll
-      for (int q = 0; q < 4; q++)
-#pragma unroll
-        for (int t = 0; t < 4; t++) Z[q][t] = 0;
-      for (int x = lane; x < 128 * 4; x += 32) sm.mk.zt[x] = 0;
+      for (int x = lane; x < 128 * 4; x += 32) {
+        sm.mk.zt[x] = 0;
+        sm.mk.zr[x] = 0;
+      }
       __syncwarp();
       for (int l = 0; l < 32 && 4 * l < n; l++) {
 #pragma unroll
@@ -276,13 +274,13 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
             const int c = ok ? mx - v[t] : 1;
             if (ok) sm.M[i * n + col] = c;
             const unsigned bz = __ballot_sync(full, ok && c == 0);
-            if (lane == l) Z[q][t] = bz;
+            if (lane == 0) sm.mk.zr[i * 4 + t] = bz;
             if (ok && c == 0) sm.mk.zt[col * 4 + (i >> 5)] |= 1u << (i & 31);
           }
         }
       }
       __syncwarp();
-      munkres_solve<int32_t>(sm.M, n, Z, sm.mk);
+      munkres_solve<int32_t>(sm.M, n, sm.mk);
       long long sc = 0;
       for (int i = lane; i < n; i += 32) {
         const int col = sm.mk.starCol[i];
@@ -350,7 +348,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
 
 size_t place_smem(int Mp) {
   return 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 8 * 128 +
-         4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 4 * 4 * 128 + 16 + 64;
+         4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 2 * 4 * 4 * 128 + 16 + 64;
 }
 
 }  // namespace
