@@ -11,6 +11,8 @@
 // kernel runs over the whole batch and marks the matrices whose range does not fit; the
 // uint16 / int32 / int64 kernels then pick up only what was marked (each is an almost-empty
 // launch when nothing was).  The solve itself is munkres.cuh.
+#include <type_traits>
+
 #include "kernels.h"
 #include "munkres.cuh"
 
@@ -46,6 +48,7 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
   size_t off = 0;
   MunkresSmem sm;
   sm.ra = smem_raw + off; off += 128 * sizeof(Pot);
+  sm.cs = smem_raw + off; off += 128 * sizeof(Pot);
   sm.starCol = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
   sm.starRow = reinterpret_cast<short*>(smem_raw + off); off += 128 * sizeof(short);
   sm.primeCol = smem_raw + off; off += 128 * sizeof(short);
@@ -64,6 +67,9 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
       sm.zr[x] = 0;
     }
     __syncwarp();
+    // cells wider than 32 bits only exist in the int64 kernel; the others saturate a difference at 2^32 - 1
+    using Diff = typename std::conditional<sizeof(CellT) == 8, unsigned long long, uint32_t>::type;
+    uint32_t acc[4] = {0, 0, 0, 0};  // zeros of the current block of 32 rows in columns lane + 32 t
     for (int l = 0; l < 32 && 4 * l < n; l++) {
       // 4 rows x 4 column blocks in flight
       long long v[4][4];
@@ -80,35 +86,54 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
       for (int q = 0; q < 4; q++) {
         const int i = 4 * l + q;
         if (i >= n) break;
-        long long mx = v[q][0];
+        Diff c[4];
+        // rows whose valid entries share one high word (the usual case: small scores) are handled on
+        // the low words alone (unsigned order == numeric order there): one redux, 32-bit differences
+        const int hi0 = __shfl_sync(full, (int)(v[q][0] >> 32), 0);  // column 0 is always valid
+        bool same = true;
 #pragma unroll
-        for (int t = 1; t < 4; t++) mx = v[q][t] > mx ? v[q][t] : mx;
-        {
-          // rows whose valid entries share one high word (the usual case: small scores) reduce
-          // on the low words with a single redux; others take the 64-bit shuffle tree
-          const int hi0 = __shfl_sync(full, (int)(v[q][0] >> 32), 0);  // column 0 is always valid
-          bool same = true;
+        for (int t = 0; t < 4; t++) same = same && (lane + 32 * t >= n || (int)(v[q][t] >> 32) == hi0);
+        if (__all_sync(full, same)) {
+          uint32_t lo[4], mx = 0;
 #pragma unroll
-          for (int t = 0; t < 4; t++) same = same && (lane + 32 * t >= n || (int)(v[q][t] >> 32) == hi0);
-          if (__all_sync(full, same)) {
-            const unsigned lo = __reduce_max_sync(full, (unsigned)(unsigned long long)mx);
-            mx = (long long)(((unsigned long long)(unsigned)hi0 << 32) | lo);
-          } else {
-            mx = warp_max_ll(mx);
+          for (int t = 0; t < 4; t++) {
+            lo[t] = lane + 32 * t < n ? (uint32_t)(unsigned long long)v[q][t] : 0u;
+            mx = max(mx, lo[t]);
+          }
+          mx = __reduce_max_sync(full, mx);
+#pragma unroll
+          for (int t = 0; t < 4; t++) c[t] = (Diff)(mx - lo[t]);
+        } else {
+          long long mx = v[q][0];
+#pragma unroll
+          for (int t = 1; t < 4; t++) mx = v[q][t] > mx ? v[q][t] : mx;
+          mx = warp_max_ll(mx);
+#pragma unroll
+          for (int t = 0; t < 4; t++) {
+            // rowmax - A: wraps only when the row's range exceeds int64, which no cell type
+            // here can hold either; such a matrix is out of the reference's domain too
+            const unsigned long long d = (unsigned long long)mx - (unsigned long long)v[q][t];
+            c[t] = sizeof(CellT) == 8 ? (Diff)d : (Diff)(d > 0xFFFFFFFFull ? 0xFFFFFFFFull : d);
           }
         }
+        const uint32_t rowBit = 1u << (i & 31);
 #pragma unroll
         for (int t = 0; t < 4; t++) {
           const int col = lane + 32 * t;
           const bool valid = col < n;
-          // rowmax - A: wraps only when the row's range exceeds int64, which no cell type
-          // here can hold either; such a matrix is out of the reference's domain too
-          const unsigned long long c = valid ? (unsigned long long)mx - (unsigned long long)v[q][t] : 0ull;
-          if (c > (unsigned long long)CellMax<CellT>::v) overflow = true;
-          if (valid) C[(size_t)i * n + col] = (CellT)c;
-          const unsigned bz = __ballot_sync(full, valid && c == 0);
+          if (valid && c[t] > (Diff)CellMax<CellT>::v) overflow = true;
+          if (valid) C[(size_t)i * n + col] = (CellT)c[t];
+          const bool z = valid && c[t] == 0;
+          const unsigned bz = __ballot_sync(full, z);
           if (lane == 0) sm.zr[i * 4 + t] = bz;
-          if (valid && c == 0) sm.zt[col * 4 + (i >> 5)] |= 1u << (i & 31);  // this lane owns column col
+          acc[t] |= z ? rowBit : 0u;  // this lane owns column col
+        }
+      }
+      if ((l & 7) == 7 || 4 * (l + 1) >= n) {  // the block of 32 rows is complete
+#pragma unroll
+        for (int t = 0; t < 4; t++) {
+          if (lane + 32 * t < n) sm.zt[(lane + 32 * t) * 4 + (l >> 3)] = acc[t];
+          acc[t] = 0;
         }
       }
     }
@@ -132,7 +157,7 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
 template <typename CellT>
 size_t munkres_smem() {
   using Pot = typename MunkresTypes<CellT>::Pot;
-  return 128 * sizeof(Pot) + 3 * 128 * sizeof(short) + 2 * 128 * 4 * sizeof(uint32_t) + 16;
+  return 2 * 128 * sizeof(Pot) + 3 * 128 * sizeof(short) + 2 * 128 * 4 * sizeof(uint32_t) + 16;
 }
 
 constexpr int kCtasPerSm = 32;  // one-warp CTAs: the hardware limit of resident CTAs per SM
@@ -156,7 +181,8 @@ cudaError_t launch_level(int n, int batch, const int64_t* A, int32_t* out, int32
 }  // namespace
 
 size_t munkres_scratch_bytes(int n, int batch, int sms) {
-  return (((size_t)batch + 255) & ~(size_t)255) + slab_region_bytes(n, sms);
+  // + the slack the last slab's vector loads may touch (munkres.cuh: kMunkresSlackRows rows of 16-bit cells)
+  return (((size_t)batch + 255) & ~(size_t)255) + slab_region_bytes(n, sms) + (size_t)kMunkresSlackRows * 128 * 2 + 256;
 }
 
 // Enqueues memset + up to four kernels; returns the number of kernels launched in *launched.

@@ -27,6 +27,8 @@
 
 namespace voda {
 
+constexpr int kMunkresSlackRows = 7;  // the vector pass of step 6 loads whole groups of 8 rows
+
 template <typename CellT>
 struct MunkresTypes {
   using Pot = int32_t;  // potentials are bounded by n * max(C) < 2^31 for 8/16-bit cells
@@ -40,11 +42,46 @@ struct MunkresTypes<int64_t> {
   using Pot = int64_t;
 };
 
+// Four adjacent cells of a row in one load (the row must start on a multiple of four cells).
+template <typename CellT>
+struct Vec4;
+template <>
+struct Vec4<uint8_t> {
+  using type = uint32_t;
+  static __device__ __forceinline__ void unpack(uint32_t w, int (&b)[4]) {
+    b[0] = (int)__byte_perm(w, 0, 0x4440);
+    b[1] = (int)__byte_perm(w, 0, 0x4441);
+    b[2] = (int)__byte_perm(w, 0, 0x4442);
+    b[3] = (int)__byte_perm(w, 0, 0x4443);
+  }
+};
+template <>
+struct Vec4<uint16_t> {
+  using type = uint2;
+  static __device__ __forceinline__ void unpack(uint2 w, int (&b)[4]) {
+    b[0] = (int)(w.x & 0xFFFFu);
+    b[1] = (int)(w.x >> 16);
+    b[2] = (int)(w.y & 0xFFFFu);
+    b[3] = (int)(w.y >> 16);
+  }
+};
+template <>
+struct Vec4<int32_t> {
+  using type = int4;
+  static __device__ __forceinline__ void unpack(int4 w, int (&b)[4]) { b[0] = w.x; b[1] = w.y; b[2] = w.z; b[3] = w.w; }
+};
+template <>
+struct Vec4<int64_t> {  // (64-bit potentials: not used by the vector path)
+  using type = int4;
+  static __device__ __forceinline__ void unpack(int4 w, int (&b)[4]) { b[0] = w.x; b[1] = w.y; b[2] = w.z; b[3] = w.w; }
+};
+
 struct MunkresSmem {
   short* starCol;   // [128] column of the star in row i, -1 if none (8-byte aligned)
   short* starRow;   // [128] row of the star in column j, -1 if none
   unsigned char* primeCol;  // [128] column of the prime in row i (valid for rows covered in this phase)
   void* ra;         // [128] row potentials (Pot)
+  void* cs;         // [128] column potentials (Pot), 16-byte aligned
   uint32_t* zr;     // [128][4] row-major zero masks: bit j of zr[i] = (value(i, j) == 0) (16-byte aligned)
   uint32_t* zt;     // [128][4] column-major zero masks: bit i of zt[j] = (value(i, j) == 0);
                     //          the caller fills both (rows and columns beyond n: no bits)
@@ -87,17 +124,18 @@ __device__ __forceinline__ T warp_min(T v) {
   return v;
 }
 
-// Solve.  C: n*n cells (row stride n) already holding rowmax_i - A[i][j]; sm.zr / sm.zt: its zero
-// masks.  On return sm.starCol[i] is the column assigned to row i.  Must be called by one full warp.
-template <typename CellT>
+// Solve.  C: n*n cells (row stride n) already holding rowmax_i - A[i][j], followed by at least
+// kMunkresSlackRows * n readable cells when the potentials are 32-bit; sm.zr / sm.zt: its zero masks.  On return sm.starCol[i] is the column assigned to row i.  Must be called by one full warp.
+// Pot: the type of the potentials; they are bounded by n * max(C), and a caller that knows its
+// cells stay below 2^31 / n can ask for 32 bits with a wider CellT.
+template <typename CellT, typename Pot = typename MunkresTypes<CellT>::Pot>
 __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresSmem& sm) {
-  using Pot = typename MunkresTypes<CellT>::Pot;
   const unsigned full = 0xffffffffu;
   const int lane = threadIdx.x & 31;
   Pot* ra = static_cast<Pot*>(sm.ra);
-  Pot cs[4] = {0, 0, 0, 0};  // potentials of columns lane + 32 t
   for (int i = lane; i < 128; i += 32) {
     ra[i] = 0;
+    static_cast<Pot*>(sm.cs)[i] = 0;
     sm.starCol[i] = -1;
     sm.starRow[i] = -1;
     sm.primeCol[i] = 0;
@@ -177,7 +215,8 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
   uint32_t ztAddr = (uint32_t)__cvta_generic_to_shared(sm.zt) + 4u * (uint32_t)(lane >> 3);
   uint32_t primeAddr = (uint32_t)__cvta_generic_to_shared(sm.primeCol);
   uint32_t ztShift = 4u * (uint32_t)(lane & 7);
-  asm volatile("" : "+r"(ztAddr), "+r"(primeAddr), "+r"(ztShift));
+  int ownBase = 4 * lane;
+  asm volatile("" : "+r"(ztAddr), "+r"(primeAddr), "+r"(ztShift), "+r"(ownBase));
 
   while (nstar < n) {
     // ---- step 4: first uncovered zero in row-major order
@@ -195,7 +234,11 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
         K[q] = me ? kNone : K[q];
         RB[q] = me ? (RB[q] | kCovered) : RB[q];
       }
-      const uint32_t hits = (word >> ztShift) & 0xFu;
+      // the column's star sits in the row just covered: that bit is always there, and it is the
+      // only one in most columns (shl clamps: the bit falls outside the nibble in every other lane)
+      uint32_t ownBit;
+      asm("shl.b32 %0, 1, %1;" : "=r"(ownBit) : "r"(row - ownBase));
+      const uint32_t hits = (word >> ztShift) & 0xFu & ~ownBit;
       if (hits) {  // zeros are sparse: most lanes, most of the time, have none in that column
         const int cb = sc << 8;
 #pragma unroll
@@ -249,32 +292,89 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
       for (int w = 0; w < 4; w++) rowCov[w] = __reduce_or_sync(full, (lane >> 3) == w ? nib : 0u);
     }
     const uint32_t own = ownCov;
-    // ---- step 6: m = smallest uncovered value; covered rows += m, uncovered columns -= m
-    bool ucol[4];
+    // ---- step 6: m = smallest uncovered value; covered rows += m, uncovered columns -= m.
+    // Column potentials live in shared memory (sm.cs): nothing of step 6 stays in registers
+    // during step 4.
+    Pot* csm = static_cast<Pot*>(sm.cs);
+    bool ucol[4];  // columns lane + 32 t that are valid and not covered
 #pragma unroll
     for (int t = 0; t < 4; t++) ucol[t] = ucolValid[t] && !((colCov[t] >> lane) & 1u);
-    Pot mn = sizeof(Pot) == 8 ? (Pot)0x7fffffffffffffffLL : (Pot)0x7fffffff;
+    const bool vec = sizeof(Pot) == 4 && (n & 3) == 0;
+    Pot mn;
     // 32-bit potentials: the minimum of every uncovered row is one redux, kept by lane l for rows
-    // l + 32 w, so that afterwards only the rows whose minimum IS m are searched for new zeros
+    // l + 32 w (rmin[w]), so that afterwards only the rows whose minimum IS m are searched for new zeros
     int rmin[4] = {0x7fffffff, 0x7fffffff, 0x7fffffff, 0x7fffffff};
+    int d[4] = {0, 0, 0, 0};  // vector path: -potential of column 4*lane + t, or a large value when covered
+    const bool colsValid = 4 * lane < n;
     if constexpr (sizeof(Pot) == 4) {
-      for (int l = 0; l < 32 && l < n; l++) {
+      if (vec) {
+        // a lane reads 4 adjacent cells of a row in one load (columns 4*lane .. 4*lane+3), kRows rows in flight
+        constexpr int kRows = kMunkresSlackRows + 1;
+        using VecT = typename Vec4<CellT>::type;
+        const int n4 = n >> 2, laneC = min(lane, n4 - 1);
+        {
+          const int4 c4 = colsValid ? reinterpret_cast<const int4*>(csm)[lane] : make_int4(0, 0, 0, 0);
+          const uint32_t cw = (lane >> 3) == 0 ? colCov[0] : (lane >> 3) == 1 ? colCov[1] : (lane >> 3) == 2 ? colCov[2] : colCov[3];
+          const uint32_t cov = (cw >> (4 * (lane & 7))) & 0xFu;
+          d[0] = (colsValid && !(cov & 1u)) ? -c4.x : 0x3fffffff;
+          d[1] = (colsValid && !(cov & 2u)) ? -c4.y : 0x3fffffff;
+          d[2] = (colsValid && !(cov & 4u)) ? -c4.z : 0x3fffffff;
+          d[3] = (colsValid && !(cov & 8u)) ? -c4.w : 0x3fffffff;
+        }
 #pragma unroll
         for (int w = 0; w < 4; w++) {
-          const int i = 32 * w + l;
-          if (i >= n || ((rowCov[w] >> l) & 1u)) continue;
-          const int rai = (int)ra[i];
-          const CellT* row = C + (size_t)i * n;
-          int v = 0x7fffffff;
+#pragma unroll 1
+          for (int c8 = 0; c8 < 32 && 32 * w + c8 < n; c8 += kRows) {
+            const int i0 = 32 * w + c8;
+            // rows beyond n count as covered; every load is unconditional (covered columns and lanes
+            // beyond the matrix carry a large d[t]; the caller's C has kRows - 1 rows of readable slack)
+            const uint32_t rw = (rowCov[w] >> c8) | (n - i0 >= kRows ? 0u : ~0u << (n - i0));
+            const VecT* p = reinterpret_cast<const VecT*>(C) + i0 * n4 + laneC;
+            VecT raw[kRows];
+            int rai[kRows];
 #pragma unroll
-          for (int t = 0; t < 4; t++)
-            if (ucol[t]) v = min(v, (int)row[lane + 32 * t] + rai - (int)cs[t]);
-          const int rm = __reduce_min_sync(full, v);
-          if (lane == l) rmin[w] = rm;
+            for (int u = 0; u < kRows; u++) {
+              raw[u] = p[u * n4];
+              rai[u] = (int)ra[i0 + u];  // ra has 128 entries
+            }
+#pragma unroll
+            for (int u = 0; u < kRows; u++) {
+              if ((rw >> u) & 1u) continue;
+              int b[4];
+              Vec4<CellT>::unpack(raw[u], b);
+              const int v = min(min(b[0] + rai[u] + d[0], b[1] + rai[u] + d[1]), min(b[2] + rai[u] + d[2], b[3] + rai[u] + d[3]));
+              const int rm = __reduce_min_sync(full, v);
+              if (lane == c8 + u) rmin[w] = rm;
+            }
+          }
+        }
+      } else {
+        int cs[4];
+#pragma unroll
+        for (int t = 0; t < 4; t++) cs[t] = ucolValid[t] ? (int)csm[lane + 32 * t] : 0;
+#pragma unroll
+        for (int w = 0; w < 4; w++) {
+#pragma unroll 1
+          for (int l = 0; l < 32 && 32 * w + l < n; l++) {
+            if ((rowCov[w] >> l) & 1u) continue;
+            const int i = 32 * w + l;
+            const int rai = (int)ra[i];
+            const CellT* row = C + (size_t)i * n;
+            int v = 0x7fffffff;
+#pragma unroll
+            for (int t = 0; t < 4; t++)
+              if (ucol[t]) v = min(v, (int)row[lane + 32 * t] + rai - cs[t]);
+            const int rm = __reduce_min_sync(full, v);
+            if (lane == l) rmin[w] = rm;
+          }
         }
       }
       mn = (Pot)__reduce_min_sync(full, min(min(rmin[0], rmin[1]), min(rmin[2], rmin[3])));
     } else {
+      Pot cs[4];
+#pragma unroll
+      for (int t = 0; t < 4; t++) cs[t] = ucolValid[t] ? csm[lane + 32 * t] : 0;
+      mn = (Pot)0x7fffffffffffffffLL;
       for (int i = 0; i < n; i++) {
         if (mask_test(rowCov, i)) continue;
         const Pot rai = ra[i];
@@ -291,9 +391,15 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
     }
     for (int i = lane; i < n; i += 32)
       if (mask_test(rowCov, i)) ra[i] += mn;
+    Pot cs[4];  // the updated potentials of columns lane + 32 t
 #pragma unroll
-    for (int t = 0; t < 4; t++)
-      if (ucol[t]) cs[t] += mn;
+    for (int t = 0; t < 4; t++) {
+      cs[t] = ucolValid[t] ? csm[lane + 32 * t] : 0;
+      if (ucol[t]) {
+        cs[t] += mn;
+        csm[lane + 32 * t] = cs[t];
+      }
+    }
     // zeros of covered rows in covered columns become positive (row-major and column-major masks)
 #pragma unroll
     for (int q = 0; q < 4; q++)
@@ -315,6 +421,10 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
     __syncwarp();
     // uncovered x uncovered cells that were equal to m become zeros
     if constexpr (sizeof(Pot) == 4) {
+      if (vec) {
+#pragma unroll
+        for (int t = 0; t < 4; t++) d[t] = d[t] == 0x3fffffff ? d[t] : d[t] - (int)mn;  // the new potentials
+      }
 #pragma unroll
       for (int w = 0; w < 4; w++) {
         unsigned rows = __ballot_sync(full, rmin[w] == (int)mn);  // only these rows hold such a cell
@@ -323,13 +433,27 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
           rows &= rows - 1;
           const int i = 32 * w + l;
           const int rai = (int)ra[i];
-          const CellT* row = C + (size_t)i * n;
+          if (vec) {
+            int b[4];
+            Vec4<CellT>::unpack(colsValid ? reinterpret_cast<const typename Vec4<CellT>::type*>(C + (size_t)i * n)[lane]
+                                          : typename Vec4<CellT>::type{}, b);
+            const uint32_t nib = (b[0] + rai + d[0] == 0 ? 1u : 0u) | (b[1] + rai + d[1] == 0 ? 2u : 0u) |
+                                 (b[2] + rai + d[2] == 0 ? 4u : 0u) | (b[3] + rai + d[3] == 0 ? 8u : 0u);
+            if (nib) {  // columns 4*lane + t: this lane's nibble of the row mask, and its own column masks
+              atomicOr(&sm.zr[i * 4 + (lane >> 3)], nib << (4 * (lane & 7)));
 #pragma unroll
-          for (int t = 0; t < 4; t++) {
-            const bool z = ucol[t] && ((int)row[lane + 32 * t] + rai - (int)cs[t] == 0);
-            const unsigned bz = __ballot_sync(full, z);
-            if (lane == 0 && bz) sm.zr[i * 4 + t] |= bz;
-            if (z) sm.zt[(lane + 32 * t) * 4 + w] |= 1u << l;
+              for (int t = 0; t < 4; t++)
+                if ((nib >> t) & 1u) sm.zt[(4 * lane + t) * 4 + w] |= 1u << l;
+            }
+          } else {
+            const CellT* row = C + (size_t)i * n;
+#pragma unroll
+            for (int t = 0; t < 4; t++) {
+              const bool z = ucol[t] && ((int)row[lane + 32 * t] + rai - (int)cs[t] == 0);
+              const unsigned bz = __ballot_sync(full, z);
+              if (lane == 0 && bz) sm.zr[i * 4 + t] |= bz;
+              if (z) sm.zt[(lane + 32 * t) * 4 + w] |= 1u << l;
+            }
           }
         }
       }

@@ -51,6 +51,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
     sm.mk.starCol = reinterpret_cast<short*>(p); p += 2 * 128;    // read as short4
     sm.mk.starRow = reinterpret_cast<short*>(p); p += 2 * 128;
     sm.mk.primeCol = p; p += 2 * 128;
+    sm.mk.cs = p; p += 8 * 128;
     sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Mp;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
     sm.mk.ra = p; p += 8 * 128;
@@ -252,6 +253,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
         sm.mk.zr[x] = 0;
       }
       __syncwarp();
+      bool wide = false;  // some cell of rowmax - M is too large for 32-bit potentials
       for (int l = 0; l < 32 && 4 * l < n; l++) {
 #pragma unroll
         for (int q = 0; q < 4; q++) {
@@ -272,6 +274,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
             const int col = lane + 32 * t;
             const bool ok = col < n;
             const int c = ok ? mx - v[t] : 1;
+            wide |= ok && (unsigned)c >= (1u << 23);
             if (ok) sm.M[i * n + col] = c;
             const unsigned bz = __ballot_sync(full, ok && c == 0);
             if (lane == 0) sm.mk.zr[i * 4 + t] = bz;
@@ -280,7 +283,10 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
         }
       }
       __syncwarp();
-      munkres_solve<int32_t>(sm.M, n, sm.mk);
+      // the potentials are bounded by n * max cell: 32 bits unless a cell reaches 2^23 (scores are sums
+      // of workers on one node: only a degenerate input gets there)
+      if (__any_sync(full, wide)) munkres_solve<int32_t, int64_t>(sm.M, n, sm.mk);
+      else munkres_solve<int32_t, int32_t>(sm.M, n, sm.mk);
       long long sc = 0;
       for (int i = lane; i < n; i += 32) {
         const int col = sm.mk.starCol[i];
@@ -347,7 +353,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
 }
 
 size_t place_smem(int Mp) {
-  return 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 8 * 128 +
+  return 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 2 * 8 * 128 +
          4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 2 * 4 * 4 * 128 + 16 + 64;
 }
 
@@ -374,7 +380,8 @@ size_t place_scratch_bytes(const PlaceArgs& a, int sms) {
   if (smem > 48 * 1024) cudaFuncSetAttribute(place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaError_t e;
   const int grid = place_grid(a, sms, smem, &e);
-  return (size_t)grid * place_slab_ints(a) * 4;
+  // + the rows the last slab's vector loads may touch beyond its matrix (munkres.cuh)
+  return (size_t)grid * place_slab_ints(a) * 4 + (size_t)kMunkresSlackRows * kMaxNodes * 4 + 256;
 }
 
 cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream) {
