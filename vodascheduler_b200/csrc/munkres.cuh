@@ -170,28 +170,25 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
   // covered so far, so nothing is stored per iteration; step 6 rebuilds the mask when it needs it.
   //
   // K[q] = (row << 16) | (first uncovered zero column of owned row q << 8) | (column of the row's
-  // star, 0xFF if it has none), or a value >= kDead when the row is covered or has no uncovered zero.
-  // RB[q] is the key of owned row q without its column; covering the row sets kCovered in it (the
-  // star's column stays readable in the low 7 bits), so that whatever is merged into K[q]
-  // afterwards stays >= kDead: no separate "row is live" test in the loop.  Inside
+  // star, 0xFF if it has none), or kNone when the row is covered or has no uncovered zero.  RB[q] is
+  // the key of owned row q without its column; `live` has a bit per owned row that is not covered.  Inside
   // a phase columns only get UNcovered and rows only get covered, so uncovering column sc turns
   // K[q] into min(K[q], key with column sc) for the live rows that have a zero there — read from
   // the column-major zero masks sm.zt — and the search "first uncovered zero in row-major order"
   // never rescans anything: it is the minimum key of the warp (one redux), which carries the row,
   // the column and the row's star.
   constexpr int kNone = 0x7fffffff;
-  constexpr int kDead = 0x7fff0000;     // keys from here up are no candidates (and have bit 7 set)
-  constexpr int kCovered = 0x7fff0080;  // OR-ed into RB[q] and K[q] when the row gets covered
   uint32_t colCov[4] = {starred[0], starred[1], starred[2], starred[3]};  // step 3
   bool ucolValid[4];
 #pragma unroll
   for (int t = 0; t < 4; t++) ucolValid[t] = lane + 32 * t < n;
   int K[4], RB[4];
+  uint32_t live = 0xFu;
   auto keys_from_masks = [&]() {
 #pragma unroll
     for (int q = 0; q < 4; q++) {
       K[q] = kNone;
-      if (RB[q] < kDead) {
+      if ((live >> q) & 1u) {
         const uint4 z = zr4[4 * lane + q];
         const uint32_t c0 = z.x & ~colCov[0], c1 = z.y & ~colCov[1], c2 = z.z & ~colCov[2], c3 = z.w & ~colCov[3];
         if (c3) K[q] = RB[q] | ((96 + __ffs(c3) - 1) << 8);
@@ -202,6 +199,7 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
     }
   };
   auto reset_phase = [&]() {  // covers = {starred columns}, no row; keys from the zero masks
+    live = 0xFu;
     const short4 sc4 = *reinterpret_cast<const short4*>(sm.starCol + 4 * lane);
     RB[0] = ((4 * lane + 0) << 16) | (sc4.x & 0xFF);
     RB[1] = ((4 * lane + 1) << 16) | (sc4.y & 0xFF);
@@ -215,8 +213,7 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
   uint32_t ztAddr = (uint32_t)__cvta_generic_to_shared(sm.zt) + 4u * (uint32_t)(lane >> 3);
   uint32_t primeAddr = (uint32_t)__cvta_generic_to_shared(sm.primeCol);
   uint32_t ztShift = 4u * (uint32_t)(lane & 7);
-  int ownBase = 4 * lane;
-  asm volatile("" : "+r"(ztAddr), "+r"(primeAddr), "+r"(ztShift), "+r"(ownBase));
+  asm volatile("" : "+r"(ztAddr), "+r"(primeAddr), "+r"(ztShift));
 
   while (nstar < n) {
     // ---- step 4: first uncovered zero in row-major order
@@ -228,17 +225,19 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
       asm volatile("ld.shared.u32 %0, [%1];" : "=r"(word) : "r"(ztAddr + 16u * (uint32_t)sc));
       // every lane stores the same value: no predicate to keep
       asm volatile("st.shared.u8 [%0], %1;" ::"r"(primeAddr + (uint32_t)row), "r"(red >> 8) : "memory");
-#pragma unroll
-      for (int q = 0; q < 4; q++) {  // the chosen key is some lane's K[q] of the row that gets covered
-        const bool me = K[q] == red;
-        K[q] = me ? kNone : K[q];
-        RB[q] = me ? (RB[q] | kCovered) : RB[q];
-      }
-      // the column's star sits in the row just covered: that bit is always there, and it is the
-      // only one in most columns (shl clamps: the bit falls outside the nibble in every other lane)
-      uint32_t ownBit;
-      asm("shl.b32 %0, 1, %1;" : "=r"(ownBit) : "r"(row - ownBase));
-      const uint32_t hits = (word >> ztShift) & 0xFu & ~ownBit;
+      // the chosen key is some lane's K[q] of the row that gets covered (two predicated operations per
+      // q; left to itself the compiler builds the new `live` from four selects)
+#define VODA_MK_COVER(q)                                                                               \
+  asm("{.reg .pred p; setp.eq.s32 p, %0, %2; @p mov.s32 %0, 0x7fffffff; @p and.b32 %1, %1, %3;}" \
+      : "+r"(K[q]), "+r"(live)                                                                        \
+      : "r"(red), "n"(~(1u << q)))
+      VODA_MK_COVER(0);
+      VODA_MK_COVER(1);
+      VODA_MK_COVER(2);
+      VODA_MK_COVER(3);
+#undef VODA_MK_COVER
+      // (the column's star sits in the row just covered: without `live` that bit would always hit)
+      const uint32_t hits = (word >> ztShift) & live;
       if (hits) {  // zeros are sparse: most lanes, most of the time, have none in that column
         const int cb = sc << 8;
 #pragma unroll
@@ -247,7 +246,7 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
       }
       continue;
     }
-    if (red < kDead) {
+    if (red != kNone) {
       // ---- step 5: augment along the alternating path that starts at the prime (row, col)
       const int row = red >> 16, col = (red >> 8) & 0xFF;
       int last = col;
@@ -278,12 +277,11 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
       uint32_t unc[4] = {0, 0, 0, 0};
 #pragma unroll
       for (int q = 0; q < 4; q++)
-        if (RB[q] >= kDead) mask_set(unc, RB[q] & 0x7f);  // a covered row holds a star
+        if (!((live >> q) & 1u)) mask_set(unc, RB[q] & 0x7f);  // a covered row holds a star
 #pragma unroll
       for (int t = 0; t < 4; t++) colCov[t] = starred[t] & ~__reduce_or_sync(full, unc[t]);
     }
-    const uint32_t ownCov = (RB[0] >= kDead ? 1u : 0u) | (RB[1] >= kDead ? 2u : 0u) | (RB[2] >= kDead ? 4u : 0u) |
-                            (RB[3] >= kDead ? 8u : 0u);
+    const uint32_t ownCov = ~live & 0xFu;
     // rebuild the uniform row-cover mask from the per-lane bits (rows 4*lane .. 4*lane+3)
     uint32_t rowCov[4];
     {
