@@ -79,7 +79,8 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
 #pragma unroll
         for (int t = 0; t < 4; t++) {
           const int col = lane + 32 * t;
-          v[q][t] = (i < n && col < n) ? M[(size_t)i * n + col] : NEG;
+          // streamed (evict-first): 13 GB of input per 100k matrices would otherwise push the C slabs out of L2
+          v[q][t] = (i < n && col < n) ? __ldcs(reinterpret_cast<const long long*>(M) + (size_t)i * n + col) : NEG;
         }
       }
 #pragma unroll
