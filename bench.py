@@ -409,7 +409,7 @@ def single_round_latency(wl, ctx, inputs, with_cpu):
     g_ref, s_ref = oracle.allocate(one, dense=True)
     assert np.array_equal(o, g_ref) and np.array_equal(s, s_ref)
     out = {"us_per_round_gpu": us, "calls": n,
-           "note": "voda_allocate on a 1-round batch (host buffers): one gathered copy each way around one launch"}
+           "note": "voda_allocate on a 1-round batch (host buffers): gathered into one page-locked block that the kernel reads and writes directly (one launch, one wait)"}
     if with_cpu:
         m = 2000
         t = time.perf_counter()

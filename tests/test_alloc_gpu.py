@@ -456,3 +456,25 @@ def test_shared_curve_pool_large_chunks(ctx, oracle):
         assert np.array_equal(s, s_ref) and np.array_equal(g, g_ref)
         h2d, d2h = ctx.copied_bytes
         assert h2d < dense.nbytes() / 3   # the curves crossed once
+
+
+@pytest.mark.parametrize("algo", ALGOS)
+def test_small_batch_paths_agree(oracle, monkeypatch, algo):
+    """A batch of a few KB is read by the kernel straight from the page-locked staging block (no
+    copies); a larger small one is gathered into one copy each way; VODA_DIRECT_BYTES=0 turns the
+    first into the second.  All three give the oracle's answer, status codes included."""
+    from vodascheduler_b200 import Context
+    batches = [synth.jobs_batch(algo, rounds=1, jobs_per_round=64, total_gpu=16),
+               synth.quirk_batch(algo, rounds=3, jobs_per_round=12, total_gpu=20),
+               synth.jobs_batch(algo, rounds=40, jobs_per_round=30, total_gpu=64, ragged=True)]
+    for direct in ("16384", "0"):
+        monkeypatch.setenv("VODA_DIRECT_BYTES", direct)
+        c = Context(0)
+        try:
+            for b in batches:
+                g_ref, s_ref = oracle.allocate(b, dense=True, threads=4)
+                for _ in range(2):  # the second call reuses the staging block
+                    g, s = c.allocate(b)
+                    assert np.array_equal(s, s_ref) and np.array_equal(g, g_ref), (algo, direct)
+        finally:
+            c.close()

@@ -38,6 +38,8 @@ struct voda_ctx {
   cudaEvent_t curves_ready = nullptr;
   void* hstage[2] = {nullptr, nullptr};   // pinned host staging per slot (packed speedup rows)
   size_t hstage_cap[2] = {0, 0};
+  size_t direct_bytes = (size_t)16 << 10;  // VODA_DIRECT_BYTES: batches up to this size are read by the kernel
+                                           // straight from the page-locked block (no copy engine at all)
   cudaEvent_t h2d_done[2] = {nullptr, nullptr};  // the slot's host staging has been consumed
   std::unique_ptr<HostPool> pool;  // host threads that pack rows (created on first use)
   bool pack_rows = false;          // VODA_PACK_ROWS=1 enables the FfDL row packing (measured slower: DESIGN.md)
@@ -302,6 +304,7 @@ int voda_ctx_create(int device, voda_ctx** out) {
   if ((e = cudaEventCreateWithFlags(&ctx->curves_ready, cudaEventDisableTiming)) != cudaSuccess) return bail(e, "cudaEventCreate");
   if (const char* v = std::getenv("VODA_PACK_ROWS")) ctx->pack_rows = std::atoi(v) != 0;
   if (const char* v = std::getenv("VODA_NARROW_COLS")) ctx->narrow_cols = std::atoi(v) != 0;
+  if (const char* v = std::getenv("VODA_DIRECT_BYTES")) ctx->direct_bytes = (size_t)std::max(0, std::atoi(v));
   *out = ctx;
   return VODA_OK;
 }
@@ -524,7 +527,7 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
         if (ctx->hstage[slot]) CU(cudaFreeHost(ctx->hstage[slot]));
         ctx->hstage[slot] = nullptr;
         ctx->hstage_cap[slot] = 0;
-        CU(cudaHostAlloc(&ctx->hstage[slot], need + need / 8, cudaHostAllocDefault));
+        CU(cudaHostAlloc(&ctx->hstage[slot], need + need / 8, cudaHostAllocMapped));
         ctx->hstage_cap[slot] = need + need / 8;
       } else {
         CU(cudaEventSynchronize(ctx->h2d_done[slot]));  // the DMA of chunk c-2 has read this slot
@@ -566,13 +569,14 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     // dozen separate copies cost more than the kernel.  Its arrays are gathered into one page-locked
     // block with the device layout and cross in ONE copy each way.
     const bool gathered = R == (int)nr && !packed && !narrow && !pool && pos <= ((size_t)256 << 10);
+    bool direct = false;
     if (gathered) {
       if (ctx->hstage_cap[slot] < pos) {
         CU(cudaStreamSynchronize(s));
         if (ctx->hstage[slot]) CU(cudaFreeHost(ctx->hstage[slot]));
         ctx->hstage[slot] = nullptr;
         ctx->hstage_cap[slot] = 0;
-        CU(cudaHostAlloc(&ctx->hstage[slot], (size_t)512 << 10, cudaHostAllocDefault));
+        CU(cudaHostAlloc(&ctx->hstage[slot], (size_t)512 << 10, cudaHostAllocMapped));
         ctx->hstage_cap[slot] = (size_t)512 << 10;
       }
       char* hs = (char*)ctx->hstage[slot];
@@ -580,7 +584,19 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
         std::memcpy(hs + cp.at, cp.src, cp.bytes);
         ctx->h2d_bytes += (int64_t)cp.bytes;
       }
-      CU(cudaMemcpyAsync(base, hs, o_og, cudaMemcpyHostToDevice, s));
+      // The smallest batches (one 64-job round is 11 KB) skip the copy engine altogether: the kernel
+      // reads the page-locked block over PCIe and writes its results into it, so the call is one
+      // launch and one wait (64 jobs: E-Tiresias 35 -> 24 us, E-SRJF 34 -> 22 us per call).  Not for
+      // AFS-L, whose kernel re-reads its curves from global memory (71 -> 93 us), nor above 16 KB
+      // (160 jobs: slower by 10 %).
+      direct = pos <= ctx->direct_bytes && b->algo != VODA_ALGO_AFSL;
+      if (direct) {
+        void* dv = nullptr;
+        CU(cudaHostGetDevicePointer(&dv, hs, 0));
+        base = (char*)dv;
+      } else {
+        CU(cudaMemcpyAsync(base, hs, o_og, cudaMemcpyHostToDevice, s));
+      }
     } else {
       for (const Copy& cp : copies) {
         CU(cudaMemcpyAsync(base + cp.at, cp.src, cp.bytes, cudaMemcpyHostToDevice, s));
@@ -623,7 +639,7 @@ int voda_allocate(voda_ctx* ctx, const voda_alloc_batch* b, int32_t* out_gpus, i
     ctx->d2h_bytes += (int64_t)(4 * nj + 4 * nr);
     if (gathered) {  // outputs come back as one block and are handed out after the wait
       char* hs = (char*)ctx->hstage[slot];
-      CU(cudaMemcpyAsync(hs + o_og, base + o_og, pos - o_og, cudaMemcpyDeviceToHost, s));
+      if (!direct) CU(cudaMemcpyAsync(hs + o_og, base + o_og, pos - o_og, cudaMemcpyDeviceToHost, s));
       CU(cudaStreamSynchronize(s));
       if (nj) std::memcpy(out_gpus + j0, hs + o_og, 4 * nj);
       std::memcpy(out_status + r0, hs + o_os, 4 * nr);
@@ -794,7 +810,7 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
     if (ctx->hstage[0]) CU(cudaFreeHost(ctx->hstage[0]));
     ctx->hstage[0] = nullptr;
     ctx->hstage_cap[0] = 0;
-    CU(cudaHostAlloc(&ctx->hstage[0], (size_t)512 << 10, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&ctx->hstage[0], (size_t)512 << 10, cudaHostAllocMapped));
     ctx->hstage_cap[0] = (size_t)512 << 10;
   }
   char* hs = (char*)ctx->hstage[0];
