@@ -126,3 +126,18 @@ def test_migration_counts_match_bookkeeping_history(ctx):
     for req in _random_rounds(9, nodes, slots, 80):
         got, want = place_round(ctx.place, ref, req, nodes, slots)
         assert got == want
+
+
+@pytest.mark.parametrize("scale", [1, 40, 300, 20000], ids=["u8", "u16-low", "u16", "i32"])
+@pytest.mark.parametrize("nodes", [16, 37, 128])
+def test_score_ranges_pick_the_cell_width(ctx, oracle, scale, nodes):
+    """The munkres step inside the placement kernel stores rowmax - score in 8-, 16- or 32-bit cells
+    depending on the score range of the round (scores are worker counts): every class, at node
+    counts that are and are not multiples of 4, against the oracle."""
+    pb = synth.place_batch(rounds=10, nodes=nodes, slots=8, jobs_per_round=nodes + 20, load=0.9)
+    pb.node_slots = (pb.node_slots * scale).astype(pb.node_slots.dtype)
+    pb.req_workers = (pb.req_workers * scale).astype(pb.req_workers.dtype)
+    pb.prev_workers = (pb.prev_workers * scale).astype(pb.prev_workers.dtype)
+    ref = oracle.place(pb, threads=8)
+    assert int(ref.score.max()) >= 8 * scale  # the class is really reached
+    _same(pb, ctx.place(pb), ref)

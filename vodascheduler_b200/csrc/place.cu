@@ -37,10 +37,71 @@ struct PlaceSmem {
   int* eNext;
   int32_t* rowmax;   // [128]
   long long* red;    // [4]
+  int* range;        // [2 per warp] min and max of the score matrix
   MunkresSmem mk;
 };
 
-__global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, int32_t* slabs, size_t slabInts) {
+// Warp 0 of the CTA: rowmax - M as CellT cells written over M's own slab (row i of the narrow matrix
+// lies inside the rows of M already consumed), the zero masks, the solve, and the total score of
+// the assignment.  Returns the score (identical in every lane).
+template <typename CellT>
+__device__ long long place_solve(const PlaceSmem& sm, int n, int lane) {
+  const unsigned full = 0xffffffffu;
+  CellT* C = reinterpret_cast<CellT*>(sm.M);
+  for (int x = lane; x < 128 * 4; x += 32) {
+    sm.mk.zt[x] = 0;
+    sm.mk.zr[x] = 0;
+  }
+  __syncwarp();
+  bool wide = false;  // some cell of rowmax - M is too large for 32-bit potentials
+  uint32_t acc[4] = {0, 0, 0, 0};  // zeros of the current block of 32 rows in columns lane + 32 t
+  for (int i = 0; i < n; i++) {
+    int v[4];
+    int mx = (int)0x80000000;
+#pragma unroll
+    for (int t = 0; t < 4; t++) {
+      const int col = lane + 32 * t;
+      v[t] = col < n ? sm.M[i * n + col] : (int)0x80000000;
+      mx = max(mx, v[t]);
+    }
+    mx = __reduce_max_sync(full, mx);
+    if (lane == 0) sm.rowmax[i] = mx;
+    const uint32_t rowBit = 1u << (i & 31);
+#pragma unroll
+    for (int t = 0; t < 4; t++) {
+      const int col = lane + 32 * t;
+      const bool ok = col < n;
+      const int c = ok ? mx - v[t] : 1;
+      wide |= ok && (unsigned)c >= (1u << 23);
+      if (ok) C[i * n + col] = (CellT)c;
+      const bool z = ok && c == 0;
+      const unsigned bz = __ballot_sync(full, z);
+      if (lane == 0) sm.mk.zr[i * 4 + t] = bz;
+      acc[t] |= z ? rowBit : 0u;  // this lane owns column col
+    }
+    if ((i & 31) == 31 || i == n - 1) {  // the block of 32 rows is complete
+#pragma unroll
+      for (int t = 0; t < 4; t++) {
+        if (lane + 32 * t < n) sm.mk.zt[(lane + 32 * t) * 4 + (i >> 5)] = acc[t];
+        acc[t] = 0;
+      }
+    }
+  }
+  __syncwarp();
+  // the potentials are bounded by n * max cell: 32 bits unless a cell reaches 2^23 (scores are sums
+  // of workers on one node: only a degenerate input gets there)
+  if (sizeof(CellT) == 4 && __any_sync(full, wide)) munkres_solve<CellT, int64_t>(C, n, sm.mk);
+  else munkres_solve<CellT, int32_t>(C, n, sm.mk);
+  long long sc = 0;
+  for (int i = lane; i < n; i += 32) sc += (long long)sm.rowmax[i] - (long long)C[i * n + sm.mk.starCol[i]];
+  for (int d = 16; d > 0; d >>= 1) sc += __shfl_xor_sync(full, sc, d);
+  return sc;
+}
+
+#ifndef VODA_PLACE_MINBLOCKS
+#define VODA_PLACE_MINBLOCKS 10  // 96 registers: 10 CTAs per SM (118 registers unbounded hold 8: 12.7 vs 9.65 ms per 20k rounds; 12 and 16 spill and are slower)
+#endif
+__global__ void __launch_bounds__(kThreads, VODA_PLACE_MINBLOCKS) place_kernel(PlaceArgs a, int Mp, int32_t* slabs, size_t slabInts) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   PlaceSmem sm;
   {
@@ -64,6 +125,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
     sm.eW = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
     sm.eNext = reinterpret_cast<int*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
     sm.rowmax = reinterpret_cast<int32_t*>(p); p += 4 * 128;
+    sm.range = reinterpret_cast<int*>(p); p += 4 * 2 * (kThreads / 32);
   }
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned full = 0xffffffffu;
@@ -247,53 +309,37 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
     }
     __syncthreads();
     // ---- ComputeMunkresMax on M (warp 0), then rename + total score ------------------------
+    // The cells of rowmax - M are bounded by max(M) - min(M): found by all threads, it picks the
+    // narrowest cell type, and the solve then works on a matrix a quarter (or half) the size of M,
+    // written over M's own slab.
+    {
+      int lo = 0x7fffffff, hi = (int)0x80000000;
+      for (int x = tid; x < n * n; x += kThreads) {
+        const int v = sm.M[x];
+        lo = min(lo, v);
+        hi = max(hi, v);
+      }
+      lo = __reduce_min_sync(full, lo);
+      hi = __reduce_max_sync(full, hi);
+      if (lane == 0) {
+        sm.range[2 * warp] = lo;
+        sm.range[2 * warp + 1] = hi;
+      }
+      __syncthreads();
+    }
     if (warp == 0) {
-      for (int x = lane; x < 128 * 4; x += 32) {
-        sm.mk.zt[x] = 0;
-        sm.mk.zr[x] = 0;
-      }
-      __syncwarp();
-      bool wide = false;  // some cell of rowmax - M is too large for 32-bit potentials
-      for (int l = 0; l < 32 && 4 * l < n; l++) {
+      int lo = sm.range[0], hi = sm.range[1];
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-          const int i = 4 * l + q;
-          if (i >= n) break;
-          int v[4];
-          int mx = (int)0x80000000;
-#pragma unroll
-          for (int t = 0; t < 4; t++) {
-            const int col = lane + 32 * t;
-            v[t] = col < n ? sm.M[i * n + col] : (int)0x80000000;
-            mx = max(mx, v[t]);
-          }
-          mx = __reduce_max_sync(full, mx);
-          if (lane == 0) sm.rowmax[i] = mx;
-#pragma unroll
-          for (int t = 0; t < 4; t++) {
-            const int col = lane + 32 * t;
-            const bool ok = col < n;
-            const int c = ok ? mx - v[t] : 1;
-            wide |= ok && (unsigned)c >= (1u << 23);
-            if (ok) sm.M[i * n + col] = c;
-            const unsigned bz = __ballot_sync(full, ok && c == 0);
-            if (lane == 0) sm.mk.zr[i * 4 + t] = bz;
-            if (ok && c == 0) sm.mk.zt[col * 4 + (i >> 5)] |= 1u << (i & 31);
-          }
-        }
+      for (int w = 1; w < kThreads / 32; w++) {
+        lo = min(lo, sm.range[2 * w]);
+        hi = max(hi, sm.range[2 * w + 1]);
       }
-      __syncwarp();
-      // the potentials are bounded by n * max cell: 32 bits unless a cell reaches 2^23 (scores are sums
-      // of workers on one node: only a degenerate input gets there)
-      if (__any_sync(full, wide)) munkres_solve<int32_t, int64_t>(sm.M, n, sm.mk);
-      else munkres_solve<int32_t, int32_t>(sm.M, n, sm.mk);
-      long long sc = 0;
-      for (int i = lane; i < n; i += 32) {
-        const int col = sm.mk.starCol[i];
-        a.phys_of_logical[n0 + i] = col;
-        sc += (long long)sm.rowmax[i] - (long long)sm.M[i * n + col];
-      }
-      for (int d = 16; d > 0; d >>= 1) sc += __shfl_xor_sync(full, sc, d);
+      const long long span = (long long)hi - (long long)lo;
+      long long sc;
+      if (span < 256) sc = place_solve<uint8_t>(sm, n, lane);
+      else if (span < 65536) sc = place_solve<uint16_t>(sm, n, lane);
+      else sc = place_solve<int32_t>(sm, n, lane);
+      for (int i = lane; i < n; i += 32) a.phys_of_logical[n0 + i] = sm.mk.starCol[i];
       if (lane == 0) {
         a.score[rd] = sc;
         a.lay_cnt[rd] = cnt;
@@ -354,7 +400,7 @@ __global__ void __launch_bounds__(kThreads) place_kernel(PlaceArgs a, int Mp, in
 
 size_t place_smem(int Mp) {
   return 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 2 * 8 * 128 +
-         4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 2 * 4 * 4 * 128 + 16 + 64;
+         4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 2 * 4 * 4 * 128 + 16 + 64 + 4 * 2 * (kThreads / 32);
 }
 
 }  // namespace
