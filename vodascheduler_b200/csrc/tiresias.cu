@@ -167,12 +167,23 @@ __global__ void __launch_bounds__(kThreads) tiresias_kernel(AllocArgs a, int Jp)
       if (n <= kRankSortMax && packedKeys) {
         // rank sort on the 64-bit keys: rank(i) = #{j : u_j < u_i or (== and j < i)}
         //                                        = #{j : u_j < u_i + [j < i]}   (u_i + 1 cannot overflow)
+        // The comparison (u_j, j) < (u_i, i) is the borrow of a three-word subtraction: four
+        // carry-chain instructions per j (the 64-bit form with the [j < i] correction took nine).
         for (int i = tid; i < n; i += nth) {
-          const unsigned long long ui = sm.ukey[i];
-          int rank = 0;
+          const uint2 ui = reinterpret_cast<const uint2*>(sm.ukey)[i];
+          int negRank = 0;
 #pragma unroll 8
-          for (int j = 0; j < n; j++) rank += sm.ukey[j] < ui + (j < i ? 1ull : 0ull) ? 1 : 0;
-          sm.perm[rank] = i;
+          for (int j = 0; j < n; j++) {
+            const uint2 uj = reinterpret_cast<const uint2*>(sm.ukey)[j];
+            asm("{ .reg .u32 t;\n\t"
+                "sub.cc.u32 t, %1, %2;\n\t"
+                "subc.cc.u32 t, %3, %4;\n\t"
+                "subc.cc.u32 t, %5, %6;\n\t"
+                "subc.u32 %0, %0, 0; }"
+                : "+r"(negRank)
+                : "r"(j), "r"(i), "r"(uj.x), "r"(ui.x), "r"(uj.y), "r"(ui.y));
+          }
+          sm.perm[-negRank] = i;
         }
         __syncthreads();
       } else if (packedKeys) {
