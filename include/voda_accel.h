@@ -80,6 +80,11 @@ void voda_ctx_copied_bytes(voda_ctx* ctx, int64_t* h2d_bytes, int64_t* d2h_bytes
 const char* voda_last_error(voda_ctx* ctx);
 const char* voda_status_str(int32_t status);
 const char* voda_version(void);
+/* sizeof() of a public struct as this library was compiled, for bindings that mirror the layouts by hand
+ * (cgo does not need it; the ctypes mirror checks itself against it): which = 0 voda_alloc_batch,
+ * 1 voda_place_batch, 2 voda_place_out, 3 voda_curve_batch, 4 voda_tick_batch, 5 voda_replay_batch,
+ * 6 voda_replay_out; anything else -> 0. */
+size_t voda_struct_size(int32_t which);
 
 /* Name <-> id of a policy.  Replaces the string switch of NewAlgorithmFactory
  * (pkg/algorithm/types.go:26-47): unknown name -> -1 (the reference returns

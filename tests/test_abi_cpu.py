@@ -65,3 +65,31 @@ def test_product_package_never_uses_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", ".cpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert not pat.search(text), f"{f} reaches into the oracle"
+
+
+def test_ctypes_mirrors_have_the_compiled_layouts(lib, tmp_path):
+    """Every struct of include/voda_accel.h that _abi.py mirrors by hand: same size as the library
+    was compiled with, and — through a C program compiled against the header here — the same offset
+    for every field."""
+    import subprocess
+    mirrors = [("voda_alloc_batch", _abi.AllocBatchStruct), ("voda_place_batch", _abi.PlaceBatchStruct),
+               ("voda_place_out", _abi.PlaceOutStruct), ("voda_curve_batch", _abi.CurveBatchStruct),
+               ("voda_tick_batch", _abi.TickBatchStruct), ("voda_replay_batch", _abi.ReplayBatchStruct),
+               ("voda_replay_out", _abi.ReplayOutStruct)]
+    for which, (cname, st) in enumerate(mirrors):
+        assert lib.voda_struct_size(which) == C.sizeof(st), cname
+    assert lib.voda_struct_size(99) == 0
+    inc = os.path.join(os.path.dirname(vbuild.HERE), "include")
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "voda_accel.h"', 'int main(void) {']
+    for cname, st in mirrors:
+        for fname, _ in st._fields_:
+            lines.append(f'  printf("{cname}.{fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "offsets.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "offsets"
+    subprocess.run(["gcc", "-I", inc, str(src), "-o", str(exe)], check=True)
+    got = dict(l.split() for l in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines())
+    for cname, st in mirrors:
+        for fname, _ in st._fields_:
+            assert int(got[f"{cname}.{fname}"]) == getattr(st, fname).offset, f"{cname}.{fname}"

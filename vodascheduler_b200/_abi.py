@@ -101,6 +101,7 @@ PROTOTYPES = {
     "voda_last_error": (C.c_char_p, [C.c_void_p]),
     "voda_status_str": (C.c_char_p, [C.c_int32]),
     "voda_version": (C.c_char_p, []),
+    "voda_struct_size": (C.c_size_t, [C.c_int32]),
     "voda_algo_from_name": (C.c_int, [C.c_char_p]),
     "voda_algo_name": (C.c_char_p, [C.c_int32]),
     "voda_algo_need_job_info": (C.c_int, [C.c_int32]),

@@ -273,7 +273,20 @@ int dispatch_alloc(voda_ctx* ctx, const AllocArgs& a, DevBuf& scratch, cudaStrea
 
 extern "C" {
 
-const char* voda_version(void) { return "vodascheduler_b200 0.1 (sm_100a)"; }
+const char* voda_version(void) { return "vodascheduler_b200 0.2 (sm_100a)"; }
+
+size_t voda_struct_size(int32_t which) {
+  switch (which) {
+    case 0: return sizeof(voda_alloc_batch);
+    case 1: return sizeof(voda_place_batch);
+    case 2: return sizeof(voda_place_out);
+    case 3: return sizeof(voda_curve_batch);
+    case 4: return sizeof(voda_tick_batch);
+    case 5: return sizeof(voda_replay_batch);
+    case 6: return sizeof(voda_replay_out);
+  }
+  return 0;
+}
 
 int voda_ctx_create(int device, voda_ctx** out) {
   if (!out) return fail(nullptr, VODA_E_INVALID, "null out pointer");
