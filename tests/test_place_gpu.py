@@ -141,3 +141,35 @@ def test_score_ranges_pick_the_cell_width(ctx, oracle, scale, nodes):
     ref = oracle.place(pb, threads=8)
     assert int(ref.score.max()) >= 8 * scale  # the class is really reached
     _same(pb, ctx.place(pb), ref)
+
+
+@pytest.mark.parametrize("split", ["0", "1"], ids=["fused", "split"])
+def test_split_and_fused_forms_agree_with_the_oracle(ctx, oracle, monkeypatch, split):
+    """Large batches without a pod table run as two kernels (score matrix, then a warp per round for the
+    assignment); VODA_PLACE_SPLIT forces either form.  Shapes: ragged node counts, every cell width,
+    refused and non-terminating rounds among solvable ones."""
+    monkeypatch.setenv("VODA_PLACE_SPLIT", split)
+    for nodes, slots, jobs, load, scale in ((16, 8, 30, 0.85, 1), (37, 8, 70, 0.95, 40), (128, 8, 200, 0.85, 1),
+                                            (128, 8, 160, 0.9, 300), (61, 4, 90, 1.2, 20000)):
+        pb = synth.place_batch(rounds=24, nodes=nodes, slots=slots, jobs_per_round=jobs, load=load)
+        pb.node_slots = (pb.node_slots * scale).astype(pb.node_slots.dtype)
+        pb.req_workers = (pb.req_workers * scale).astype(pb.req_workers.dtype)
+        pb.prev_workers = (pb.prev_workers * scale).astype(pb.prev_workers.dtype)
+        _same(pb, ctx.place(pb), oracle.place(pb, threads=8))
+    rounds = [
+        dict(nodes=[8, 8], requests=[6, 6, 4], prev=[[(0, 6)], [(1, 6), (2, 2)]]),
+        dict(nodes=[8, 8], requests=[16, 1]),
+        dict(nodes=[], requests=[1, 2]),
+        dict(nodes=[4, 4, 4], requests=[5, 5, 2], prev=[[(0, 4)], [(0, 1), (1, 3)], [(2, 2)]]),
+        dict(nodes=[8], requests=[]),
+        dict(nodes=[0, 0], requests=[1]),
+    ]
+    pb = place_batch_from(rounds)
+    _same(pb, ctx.place(pb), oracle.place(pb))
+
+
+def test_split_form_large_batch(ctx, oracle):
+    """A batch large enough to take the split form by itself (and more than one 1 GiB sub-batch of
+    slabs would need only at 16k+ rounds of 128 nodes: 6 000 rounds stay in one)."""
+    pb = synth.place_batch(rounds=6000, nodes=32, slots=8, jobs_per_round=50, load=0.9)
+    _same(pb, ctx.place(pb), oracle.place(pb, threads=16))

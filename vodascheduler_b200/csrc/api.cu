@@ -762,8 +762,9 @@ static int dispatch_place(voda_ctx* ctx, const PlaceArgs& a, DevBuf& scratch, cu
     return fail(ctx, VODA_E_UNSUPPORTED, "placement: too many requests per round for one CTA's shared memory");
   int rc = ensure(ctx, scratch, place_scratch_bytes(a, ctx->sms), stream);
   if (rc) return rc;
-  CU(launch_place(a, ctx->sms, scratch.p, stream));
-  ctx->launches += 1;
+  int launched = 0;
+  CU(launch_place(a, ctx->sms, scratch.p, stream, &launched));
+  ctx->launches += launched;
   return VODA_OK;
 }
 

@@ -35,7 +35,7 @@ cudaError_t launch_munkres(int n, int batch, const int64_t* A, int32_t* out, int
 // bestFit + score + munkres placement rounds (place.cu)
 size_t place_smem_bytes(const PlaceArgs& a);
 size_t place_scratch_bytes(const PlaceArgs& a, int sms);
-cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream);
+cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream, int* launched);
 
 // speedup-curve builder (curves.cu)
 cudaError_t launch_curves(int jobs, const int32_t* rec_off, const int32_t* workers, const double* t, int W,

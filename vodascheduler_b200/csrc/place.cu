@@ -101,21 +101,34 @@ __device__ long long place_solve(const PlaceSmem& sm, int n, int lane) {
 #ifndef VODA_PLACE_MINBLOCKS
 #define VODA_PLACE_MINBLOCKS 10  // 96 registers: 10 CTAs per SM (118 registers unbounded hold 8: 12.7 vs 9.65 ms per 20k rounds; 12 and 16 spill and are slower)
 #endif
-__global__ void __launch_bounds__(kThreads, VODA_PLACE_MINBLOCKS) place_kernel(PlaceArgs a, int Mp, int32_t* slabs, size_t slabInts) {
+constexpr size_t kMunkresSmemBytes = 16 + 2 * 4 * 4 * 128 + 3 * 2 * 128 + 2 * 8 * 128;
+// The solver's shared-memory state, from the next 16-byte boundary at or after p.
+__device__ __forceinline__ void carve_munkres(MunkresSmem& mk, unsigned char* p) {
+  p = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(p) + 15) & ~(uintptr_t)15);
+  mk.zr = reinterpret_cast<uint32_t*>(p); p += 4 * 4 * 128;  // read as uint4
+  mk.zt = reinterpret_cast<uint32_t*>(p); p += 4 * 4 * 128;
+  mk.cs = p; p += 8 * 128;                                   // read as int4
+  mk.ra = p; p += 8 * 128;
+  mk.starCol = reinterpret_cast<short*>(p); p += 2 * 128;    // read as short4
+  mk.starRow = reinterpret_cast<short*>(p); p += 2 * 128;
+  mk.primeCol = p; p += 2 * 128;
+}
+
+// SPLIT: the kernel stops after the score matrix (one slab per ROUND of [r0, r1)) and leaves the
+// assignment to place_solve_kernel, which runs a warp per round at twice the residency; the fused form
+// (one slab per CTA) serves small batches, where a second launch would cost more than it gains, and
+// rounds with a pod table, whose migration counts need the layout this kernel still holds.
+constexpr int kPending = -2;  // status of a round whose assignment place_solve_kernel has yet to compute
+template <bool SPLIT>
+__global__ void __launch_bounds__(kThreads, SPLIT ? 1 : VODA_PLACE_MINBLOCKS)
+    place_kernel(PlaceArgs a, int Mp, int32_t* slabs, size_t slabInts, int r0, int r1) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   PlaceSmem sm;
   {
     unsigned char* p = smem_raw;
     sm.M = slabs + (size_t)blockIdx.x * slabInts;
-    sm.mk.zr = reinterpret_cast<uint32_t*>(p); p += 4 * 4 * 128;  // read as uint4: 16-byte aligned, so first
-    sm.mk.zt = reinterpret_cast<uint32_t*>(p); p += 4 * 4 * 128;
-    sm.mk.starCol = reinterpret_cast<short*>(p); p += 2 * 128;    // read as short4
-    sm.mk.starRow = reinterpret_cast<short*>(p); p += 2 * 128;
-    sm.mk.primeCol = p; p += 2 * 128;
-    sm.mk.cs = p; p += 8 * 128;
     sm.khi = reinterpret_cast<int64_t*>(p); p += 8 * (size_t)Mp;
     sm.red = reinterpret_cast<long long*>(p); p += 8 * 4;
-    sm.mk.ra = p; p += 8 * 128;
     sm.klo = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Mp;
     sm.perm = reinterpret_cast<int*>(p); p += 4 * (size_t)Mp;
     sm.workers = reinterpret_cast<int32_t*>(p); p += 4 * (size_t)Mp;
@@ -126,11 +139,13 @@ __global__ void __launch_bounds__(kThreads, VODA_PLACE_MINBLOCKS) place_kernel(P
     sm.eNext = reinterpret_cast<int*>(p); p += 4 * (size_t)(Mp + kMaxNodes);
     sm.rowmax = reinterpret_cast<int32_t*>(p); p += 4 * 128;
     sm.range = reinterpret_cast<int*>(p); p += 4 * 2 * (kThreads / 32);
+    if (!SPLIT) carve_munkres(sm.mk, p);  // last: the split form does not allocate it
   }
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const unsigned full = 0xffffffffu;
 
-  for (int rd = blockIdx.x; rd < a.rounds; rd += gridDim.x) {
+  for (int rd = r0 + blockIdx.x; rd < r1; rd += gridDim.x) {
+    if (SPLIT) sm.M = slabs + (size_t)(rd - r0) * slabInts;
     const int n0 = a.node_off[rd], n = a.node_off[rd + 1] - n0;
     const int q0 = a.req_off[rd], m = a.req_off[rd + 1] - q0;
     const int e0 = q0 + n0;
@@ -308,6 +323,14 @@ __global__ void __launch_bounds__(kThreads, VODA_PLACE_MINBLOCKS) place_kernel(P
       }
     }
     __syncthreads();
+    if (SPLIT) {  // the matrix is complete (barrier above): the rest of the round is place_solve_kernel's
+      if (tid == 0) {
+        a.lay_cnt[rd] = cnt;
+        a.cross[rd] = (int)sm.red[2];
+        a.status[rd] = kPending;
+      }
+      continue;
+    }
     // ---- ComputeMunkresMax on M (warp 0), then rename + total score ------------------------
     // The cells of rowmax - M are bounded by max(M) - min(M): found by all threads, it picks the
     // narrowest cell type, and the solve then works on a matrix a quarter (or half) the size of M,
@@ -398,9 +421,49 @@ __global__ void __launch_bounds__(kThreads, VODA_PLACE_MINBLOCKS) place_kernel(P
   }
 }
 
-size_t place_smem(int Mp) {
-  return 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 2 * 8 * 128 +
-         4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 3 * 2 * 128 + 2 * 4 * 4 * 128 + 16 + 64 + 4 * 2 * (kThreads / 32);
+// The assignment half of the split form: ONE WARP per round (a one-warp CTA, so that an SM holds twice as
+// many rounds as the fused kernel does).  Reads the score matrix place_kernel<true> left in the round's
+// slab and writes the binding, the total score and the final status.
+constexpr size_t kSolveSmemBytes = kMunkresSmemBytes + 4 * 128;
+#ifndef VODA_SOLVE_MINBLOCKS
+#define VODA_SOLVE_MINBLOCKS 20  // 96 registers: 20 one-warp CTAs per SM (16 / 20 / 24 / 32: 6.89 / 6.47 / 6.46 / 6.50 ms per 20k rounds)
+#endif
+__global__ void __launch_bounds__(32, VODA_SOLVE_MINBLOCKS) place_solve_kernel(PlaceArgs a, int32_t* slabs, size_t slabInts, int r0, int r1) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  PlaceSmem sm{};
+  sm.rowmax = reinterpret_cast<int32_t*>(smem_raw);
+  carve_munkres(sm.mk, smem_raw + 4 * 128);
+  const int lane = threadIdx.x;
+  const unsigned full = 0xffffffffu;
+  for (int rd = r0 + blockIdx.x; rd < r1; rd += gridDim.x) {
+    if (a.status[rd] != kPending) continue;  // refused or empty: place_kernel has written the outcome
+    const int n0 = a.node_off[rd], n = a.node_off[rd + 1] - n0;
+    sm.M = slabs + (size_t)(rd - r0) * slabInts;
+    int lo = 0x7fffffff, hi = (int)0x80000000;
+    for (int x = lane; x < n * n; x += 32) {
+      const int v = sm.M[x];
+      lo = min(lo, v);
+      hi = max(hi, v);
+    }
+    lo = __reduce_min_sync(full, lo);
+    hi = __reduce_max_sync(full, hi);
+    const long long span = (long long)hi - (long long)lo;
+    long long sc;
+    if (span < 256) sc = place_solve<uint8_t>(sm, n, lane);
+    else if (span < 65536) sc = place_solve<uint16_t>(sm, n, lane);
+    else sc = place_solve<int32_t>(sm, n, lane);
+    for (int i = lane; i < n; i += 32) a.phys_of_logical[n0 + i] = sm.mk.starCol[i];
+    if (lane == 0) {
+      a.score[rd] = sc;
+      a.status[rd] = VODA_ST_OK;
+    }
+    __syncwarp();
+  }
+}
+
+size_t place_smem(int Mp, bool split = false) {
+  return 16 + (size_t)Mp * (8 + 4 * 4) + 8 * 4 + 4 * 4 * (size_t)(Mp + kMaxNodes) + 4 * 128 + 4 * 2 * (kThreads / 32) + 64 +
+         (split ? 0 : kMunkresSmemBytes);
 }
 
 }  // namespace
@@ -409,39 +472,81 @@ size_t place_smem_bytes(const PlaceArgs& a) { return place_smem(next_pow2(a.max_
 
 static size_t place_slab_ints(const PlaceArgs& a) { return (((size_t)a.max_nodes * a.max_nodes) + 63) & ~(size_t)63; }
 
-static int place_grid(const PlaceArgs& a, int sms, size_t smem, cudaError_t* err) {
+template <bool SPLIT>
+static int place_grid(const PlaceArgs& a, int rounds, int sms, size_t smem, cudaError_t* err) {
   int perSm = 0;
-  *err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, place_kernel, kThreads, smem);
+  *err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&perSm, place_kernel<SPLIT>, kThreads, smem);
   if (perSm < 1) perSm = 1;
   if (const char* v = std::getenv("VODA_PLACE_CTAS")) perSm = std::max(1, std::min(perSm, std::atoi(v)));
   int grid = sms * perSm;
-  if (a.rounds < grid) grid = a.rounds;
+  if (rounds < grid) grid = rounds;
   return grid;
 }
 
-// bytes of global scratch the launch needs (score-matrix slabs, one per CTA)
-size_t place_scratch_bytes(const PlaceArgs& a, int sms) {
-  const int Mp = next_pow2(a.max_requests > 0 ? a.max_requests : 1);
-  const size_t smem = place_smem(Mp);
-  if (smem > 48 * 1024) cudaFuncSetAttribute(place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  cudaError_t e;
-  const int grid = place_grid(a, sms, smem, &e);
-  // + the rows the last slab's vector loads may touch beyond its matrix (munkres.cuh)
-  return (size_t)grid * place_slab_ints(a) * 4 + (size_t)kMunkresSlackRows * kMaxNodes * 4 + 256;
+// The split form pays a second launch and a slab per round: it is used for batches of at least a few
+// waves of the fused kernel, without a pod table (the migration counts need the fused kernel's state).
+static bool place_split(const PlaceArgs& a, int sms) {
+  if (const char* v = std::getenv("VODA_PLACE_SPLIT")) return std::atoi(v) != 0 && !a.pods_off;
+  return !a.pods_off && a.rounds >= 4 * 10 * sms;
+}
+// rounds of the split form processed per pair of launches: their slabs may take 1 GiB
+static int place_split_rounds(const PlaceArgs& a) {
+  const size_t per = place_slab_ints(a) * 4;
+  return (int)std::max<size_t>(1, std::min<size_t>((size_t)a.rounds, ((size_t)1 << 30) / per));
 }
 
-cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream) {
+// bytes of global scratch the launch needs (score-matrix slabs: one per CTA, or one per round of a sub-batch)
+size_t place_scratch_bytes(const PlaceArgs& a, int sms) {
   const int Mp = next_pow2(a.max_requests > 0 ? a.max_requests : 1);
+  // + the rows the last slab's vector loads may touch beyond its matrix (munkres.cuh)
+  const size_t slack = (size_t)kMunkresSlackRows * kMaxNodes * 4 + 256;
+  if (place_split(a, sms)) return (size_t)place_split_rounds(a) * place_slab_ints(a) * 4 + slack;
   const size_t smem = place_smem(Mp);
+  if (smem > 48 * 1024) cudaFuncSetAttribute(place_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e;
+  const int grid = place_grid<false>(a, a.rounds, sms, smem, &e);
+  return (size_t)grid * place_slab_ints(a) * 4 + slack;
+}
+
+// Enqueues the placement of every round; *launched = kernels launched.
+cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream, int* launched) {
+  const int Mp = next_pow2(a.max_requests > 0 ? a.max_requests : 1);
+  int32_t* slabs = static_cast<int32_t*>(scratch);
+  cudaError_t e;
+  *launched = 0;
+  if (!place_split(a, sms)) {
+    const size_t smem = place_smem(Mp);
+    if (smem > 48 * 1024) {
+      e = cudaFuncSetAttribute(place_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      if (e != cudaSuccess) return e;
+    }
+    const int grid = place_grid<false>(a, a.rounds, sms, smem, &e);
+    if (e != cudaSuccess) return e;
+    place_kernel<false><<<grid, kThreads, smem, stream>>>(a, Mp, slabs, place_slab_ints(a), 0, a.rounds);
+    *launched = 1;
+    return cudaGetLastError();
+  }
+  const size_t smem = place_smem(Mp, true);
   if (smem > 48 * 1024) {
-    cudaError_t e = cudaFuncSetAttribute(place_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    e = cudaFuncSetAttribute(place_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  cudaError_t e;
-  const int grid = place_grid(a, sms, smem, &e);
+  int solvePerSm = 0;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&solvePerSm, place_solve_kernel, 32, kSolveSmemBytes);
   if (e != cudaSuccess) return e;
-  place_kernel<<<grid, kThreads, smem, stream>>>(a, Mp, static_cast<int32_t*>(scratch), place_slab_ints(a));
-  return cudaGetLastError();
+  if (solvePerSm < 1) solvePerSm = 1;
+  const int sub = place_split_rounds(a);
+  for (int r0 = 0; r0 < a.rounds; r0 += sub) {
+    const int r1 = std::min(a.rounds, r0 + sub);
+    const int grid = place_grid<true>(a, r1 - r0, sms, smem, &e);
+    if (e != cudaSuccess) return e;
+    place_kernel<true><<<grid, kThreads, smem, stream>>>(a, Mp, slabs, place_slab_ints(a), r0, r1);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    place_solve_kernel<<<std::min(r1 - r0, sms * solvePerSm), 32, kSolveSmemBytes, stream>>>(a, slabs, place_slab_ints(a), r0, r1);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+    *launched += 2;
+  }
+  return cudaSuccess;
 }
 
 }  // namespace voda
