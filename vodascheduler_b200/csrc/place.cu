@@ -435,6 +435,8 @@ __global__ void __launch_bounds__(32, VODA_SOLVE_MINBLOCKS) place_solve_kernel(P
   carve_munkres(sm.mk, smem_raw + 4 * 128);
   const int lane = threadIdx.x;
   const unsigned full = 0xffffffffu;
+  // one CTA per round, not a persistent grid: rounds differ in length by a factor of several, and the
+  // hardware hands the next round to whichever SM has room
   for (int rd = r0 + blockIdx.x; rd < r1; rd += gridDim.x) {
     if (a.status[rd] != kPending) continue;  // refused or empty: place_kernel has written the outcome
     const int n0 = a.node_off[rd], n = a.node_off[rd + 1] - n0;
@@ -489,10 +491,12 @@ static bool place_split(const PlaceArgs& a, int sms) {
   if (const char* v = std::getenv("VODA_PLACE_SPLIT")) return std::atoi(v) != 0 && !a.pods_off;
   return !a.pods_off && a.rounds >= 4 * 10 * sms;
 }
-// rounds of the split form processed per pair of launches: their slabs may take 1 GiB
+// rounds of the split form processed per pair of launches: their slabs may take 2 GiB; equal sub-batches
 static int place_split_rounds(const PlaceArgs& a) {
   const size_t per = place_slab_ints(a) * 4;
-  return (int)std::max<size_t>(1, std::min<size_t>((size_t)a.rounds, ((size_t)1 << 30) / per));
+  const size_t cap = std::max<size_t>(1, ((size_t)2 << 30) / per);
+  const size_t parts = ((size_t)a.rounds + cap - 1) / cap;
+  return (int)(((size_t)a.rounds + parts - 1) / parts);
 }
 
 // bytes of global scratch the launch needs (score-matrix slabs: one per CTA, or one per round of a sub-batch)
@@ -531,10 +535,6 @@ cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_
     e = cudaFuncSetAttribute(place_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  int solvePerSm = 0;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&solvePerSm, place_solve_kernel, 32, kSolveSmemBytes);
-  if (e != cudaSuccess) return e;
-  if (solvePerSm < 1) solvePerSm = 1;
   const int sub = place_split_rounds(a);
   for (int r0 = 0; r0 < a.rounds; r0 += sub) {
     const int r1 = std::min(a.rounds, r0 + sub);
@@ -542,7 +542,7 @@ cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_
     if (e != cudaSuccess) return e;
     place_kernel<true><<<grid, kThreads, smem, stream>>>(a, Mp, slabs, place_slab_ints(a), r0, r1);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
-    place_solve_kernel<<<std::min(r1 - r0, sms * solvePerSm), 32, kSolveSmemBytes, stream>>>(a, slabs, place_slab_ints(a), r0, r1);
+    place_solve_kernel<<<r1 - r0, 32, kSolveSmemBytes, stream>>>(a, slabs, place_slab_ints(a), r0, r1);
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
     *launched += 2;
   }
