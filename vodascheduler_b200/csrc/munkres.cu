@@ -6,7 +6,7 @@
 // C is only read again by step 6 (a handful of times per matrix), so it lives in a per-CTA
 // slab of global scratch that stays L2-resident (16 KB per matrix as uint8), NOT in shared
 // memory: the solve is a chain of dependent warp steps, throughput comes from how many
-// matrices an SM works on at once, and with ~5 KB of shared memory per matrix that is the
+// matrices an SM works on at once, and with 5.9 KB of shared memory per matrix that is the
 // hardware limit of 32 one-warp CTAs per SM.  The cell type is found by trying: the uint8
 // kernel runs over the whole batch and marks the matrices whose range does not fit; the
 // uint16 / int32 / int64 kernels then pick up only what was marked (each is an almost-empty

@@ -14,6 +14,9 @@
 // Reference quirks kept: the last chunk of a split job records the WHOLE request (Q11, :479)
 // so freeSlots can go negative, and the loop that never ends once a request meets a cluster
 // without usable slots (Q12) is cut with VODA_ST_NONTERMINATING.
+// Large batches without a pod table run in a split form instead: place_kernel<true> stops after the
+// score matrix (a slab per round) and place_solve_kernel solves with one warp per round, which doubles
+// the rounds an SM works on during the assignment (see launch_place).
 #include "kernels.h"
 #include "munkres.cuh"
 
