@@ -541,14 +541,15 @@ def run_chain(name, wl, ctx, env, steps, warmup, e2e_steps, with_cpu):
     hab = ctx.pin_batch(ab)
     h_g = ctx.pinned((ab.jobs,), np.int32)
     h_s = ctx.pinned((R,), np.int32)
-    hout = PlaceOut(R, pb.nodes, pb.requests)
+    hpb = ctx.pin_place_batch(pb)
+    hout = ctx.pinned_place_out(R, pb.nodes, pb.requests)
     moved = [0, 0]
 
     def step_e2e():
         ctx.allocate(hab, h_g, h_s)
         a, b = ctx.copied_bytes
-        pb.req_workers = h_g
-        ctx.place(pb, hout)
+        hpb.req_workers = h_g  # the allocation result (page-locked) is the request list
+        ctx.place(hpb, hout)
         moved[0], moved[1] = a, b
 
     e2e_ms = time_host_steps(env, step_e2e, e2e_steps, warmup=1)
@@ -615,8 +616,9 @@ def run_place(name, wl, ctx, env, steps, warmup, e2e_steps, with_cpu):
     from vodascheduler_b200.batch import PlaceOut
     R = wl["rounds"]
     inputs = synth.place_batch(R, wl["nodes"], wl["slots"], wl["jobs"], seed=synth.SEED + env.rank)
-    pout = PlaceOut(R, inputs.nodes, inputs.requests)
-    e2e_ms = time_host_steps(env, lambda: ctx.place(inputs, pout), e2e_steps)
+    pout = ctx.pinned_place_out(R, inputs.nodes, inputs.requests)
+    hin = ctx.pin_place_batch(inputs)  # page-locked, like every other end-to-end input
+    e2e_ms = time_host_steps(env, lambda: ctx.place(hin, pout), e2e_steps)
     (e2e_ms,) = env.max_over_ranks(e2e_ms)
     if env.rank != 0:
         return None

@@ -173,3 +173,13 @@ def test_split_form_large_batch(ctx, oracle):
     slabs would need only at 16k+ rounds of 128 nodes: 6 000 rounds stay in one)."""
     pb = synth.place_batch(rounds=6000, nodes=32, slots=8, jobs_per_round=50, load=0.9)
     _same(pb, ctx.place(pb), oracle.place(pb, threads=16))
+
+
+def test_chunked_host_path_equals_single_shot(ctx, oracle):
+    """voda_place on a batch large enough for the two-stream chunked path (at least eight waves of
+    rounds) gives what the oracle computes, ragged round sizes included."""
+    import torch
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    rounds = 2 * max(2 * 10 * sms, 1) * 2 + 37  # >= 2 chunks of >= 2 * 10 * sms rounds, not a multiple
+    pb = synth.place_batch(rounds=rounds, nodes=12, slots=8, jobs_per_round=20, load=0.9)
+    _same(pb, ctx.place(pb), oracle.place(pb, threads=16))

@@ -216,6 +216,27 @@ class Context:
             self._lib.voda_host_free(p)
         self._pins = []
 
+    def pin_place_batch(self, batch: PlaceBatch) -> PlaceBatch:
+        """Copy of a placement batch whose arrays live in page-locked memory."""
+        b = PlaceBatch.__new__(PlaceBatch)
+        b.__dict__.update(batch.__dict__)
+        for name, v in batch.__dict__.items():
+            if isinstance(v, np.ndarray):
+                pv = self.pinned(v.shape, v.dtype)
+                pv[...] = v
+                setattr(b, name, pv)
+        return b
+
+    def pinned_place_out(self, rounds, nodes, requests) -> PlaceOut:
+        """PlaceOut whose arrays live in page-locked memory."""
+        out = PlaceOut(rounds, nodes, requests)
+        for name, v in list(out.__dict__.items()):
+            if isinstance(v, np.ndarray):
+                pv = self.pinned(v.shape, v.dtype)
+                pv[...] = v
+                setattr(out, name, pv)
+        return out
+
     def pin_batch(self, batch: AllocBatch) -> AllocBatch:
         """Copy of `batch` whose arrays live in page-locked memory."""
         from .batch import _ALLOC_ARRAYS

@@ -755,15 +755,17 @@ static PlaceArgs make_place_args(const voda_place_batch* b, const voda_place_out
   return a;
 }
 
-static int dispatch_place(voda_ctx* ctx, const PlaceArgs& a, DevBuf& scratch, cudaStream_t stream) {
-  if (a.rounds == 0) return VODA_OK;
+static int dispatch_place(voda_ctx* ctx, const PlaceArgs& a, DevBuf& scratch, cudaStream_t stream, int first = 0,
+                          int last = -1) {
+  if (last < 0) last = a.rounds;
+  if (last <= first) return VODA_OK;
   if (a.max_nodes > 128) return fail(ctx, VODA_E_UNSUPPORTED, "placement: more than 128 nodes per round");
   if (place_smem_bytes(a) > 220 * 1024)
     return fail(ctx, VODA_E_UNSUPPORTED, "placement: too many requests per round for one CTA's shared memory");
-  int rc = ensure(ctx, scratch, place_scratch_bytes(a, ctx->sms), stream);
+  int rc = ensure(ctx, scratch, place_scratch_bytes(a, ctx->sms, last - first), stream);
   if (rc) return rc;
   int launched = 0;
-  CU(launch_place(a, ctx->sms, scratch.p, stream, &launched));
+  CU(launch_place(a, ctx->sms, scratch.p, stream, &launched, first, last));
   ctx->launches += launched;
   return VODA_OK;
 }
@@ -828,8 +830,16 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
     ctx->hstage_cap[0] = (size_t)512 << 10;
   }
   char* hs = (char*)ctx->hstage[0];
+  // chunks of at least two waves of the solve kernel, a quarter of the batch at most
+  int parts = 4;
+  if (const char* v = std::getenv("VODA_PLACE_CHUNKS")) parts = std::max(1, std::atoi(v));
+  const int chunkRounds = std::max(2 * 10 * ctx->sms, (R + parts - 1) / parts);
+  const bool chunked = !gathered && !pods && R >= 2 * chunkRounds;
+  ctx->h2d_bytes = 0;
+  ctx->d2h_bytes = 0;
   auto h2d = [&](size_t at, const void* src, size_t bytes) -> cudaError_t {
     if (!bytes) return cudaSuccess;
+    ctx->h2d_bytes += (int64_t)bytes;
     if (gathered) {
       std::memcpy(hs + at, src, bytes);
       return cudaSuccess;
@@ -837,12 +847,14 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
     return cudaMemcpyAsync(base + at, src, bytes, cudaMemcpyHostToDevice, s);
   };
   CU(h2d(i_no, b->node_off, 4 * (size_t)(R + 1)));
-  CU(h2d(i_ns, b->node_slots, 4 * (size_t)nodes));
   CU(h2d(i_ro, b->req_off, 4 * (size_t)(R + 1)));
-  CU(h2d(i_rw, b->req_workers, 4 * (size_t)reqs));
   CU(h2d(i_po, b->prev_off, 4 * (size_t)(nodes + 1)));
-  CU(h2d(i_pj, b->prev_job, 4 * (size_t)prevs));
-  CU(h2d(i_pw, b->prev_workers, 4 * (size_t)prevs));
+  if (!chunked) {
+    CU(h2d(i_ns, b->node_slots, 4 * (size_t)nodes));
+    CU(h2d(i_rw, b->req_workers, 4 * (size_t)reqs));
+    CU(h2d(i_pj, b->prev_job, 4 * (size_t)prevs));
+    CU(h2d(i_pw, b->prev_workers, 4 * (size_t)prevs));
+  }
   if (pods) {
     CU(h2d(i_qo, b->pods_off, 4 * (size_t)(reqs + 1)));
     CU(h2d(i_qn, b->pods_node, 4 * (size_t)podRuns));
@@ -863,6 +875,49 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   a.phys_of_logical = (int32_t*)(base + o_ph); a.free_slots = (int32_t*)(base + o_fr); a.lay_cnt = (int32_t*)(base + o_lc);
   a.lay_node = (int32_t*)(base + o_ln); a.lay_job = (int32_t*)(base + o_lj); a.lay_workers = (int32_t*)(base + o_lw);
   a.score = (long long*)(base + o_sc); a.cross = (int32_t*)(base + o_cr); a.status = (int32_t*)(base + o_st);
+  if (chunked) {
+    // Large batches: the three offset arrays have crossed (above, on stream 0); the data of every chunk
+    // of rounds goes to its place in the same device layout on one of two streams, so that the copies of
+    // one chunk run under the kernels of the other.
+    CU(cudaEventRecord(ctx->h2d_done[0], ctx->pipe[0]));
+    CU(cudaStreamWaitEvent(ctx->pipe[1], ctx->h2d_done[0], 0));
+    int c = 0;
+    for (int r0 = 0; r0 < R; r0 += chunkRounds, c++) {
+      const int r1 = std::min(R, r0 + chunkRounds);
+      cudaStream_t cs = ctx->pipe[c & 1];
+      const size_t n0 = (size_t)b->node_off[r0], n1 = (size_t)b->node_off[r1], q0 = (size_t)b->req_off[r0], q1 = (size_t)b->req_off[r1];
+      const size_t p0 = (size_t)b->prev_off[n0], p1 = (size_t)b->prev_off[n1];
+      auto in = [&](size_t at, const int32_t* src, size_t i0, size_t i1) -> cudaError_t {
+        if (i1 <= i0) return cudaSuccess;
+        ctx->h2d_bytes += (int64_t)(4 * (i1 - i0));
+        return cudaMemcpyAsync(base + at + 4 * i0, src + i0, 4 * (i1 - i0), cudaMemcpyHostToDevice, cs);
+      };
+      CU(in(i_ns, b->node_slots, n0, n1));
+      CU(in(i_rw, b->req_workers, q0, q1));
+      CU(in(i_pj, b->prev_job, p0, p1));
+      CU(in(i_pw, b->prev_workers, p0, p1));
+      rc = dispatch_place(ctx, a, ctx->pipe_scratch[c & 1], cs, r0, r1);
+      if (rc) return rc;
+      auto out = [&](void* dst, size_t at, size_t width, size_t i0, size_t i1) -> cudaError_t {
+        if (!dst || i1 <= i0) return cudaSuccess;
+        ctx->d2h_bytes += (int64_t)(width * (i1 - i0));
+        return cudaMemcpyAsync((char*)dst + width * i0, base + at + width * i0, width * (i1 - i0), cudaMemcpyDeviceToHost, cs);
+      };
+      CU(out(o->phys_of_logical, o_ph, 4, n0, n1));
+      CU(out(o->free_slots, o_fr, 4, n0, n1));
+      CU(out(o->lay_cnt, o_lc, 4, (size_t)r0, (size_t)r1));
+      CU(out(o->lay_node, o_ln, 4, q0 + n0, q1 + n1));
+      CU(out(o->lay_job, o_lj, 4, q0 + n0, q1 + n1));
+      CU(out(o->lay_workers, o_lw, 4, q0 + n0, q1 + n1));
+      CU(out(o->score, o_sc, 8, (size_t)r0, (size_t)r1));
+      CU(out(o->cross, o_cr, 4, (size_t)r0, (size_t)r1));
+      CU(out(o->status, o_st, 4, (size_t)r0, (size_t)r1));
+    }
+    CU(cudaStreamSynchronize(ctx->pipe[0]));
+    CU(cudaStreamSynchronize(ctx->pipe[1]));
+    guard.armed = false;
+    return VODA_OK;
+  }
   if (gathered) CU(cudaMemcpyAsync(base, hs, o_mw, cudaMemcpyHostToDevice, s));  // every input, one copy
   rc = dispatch_place(ctx, a, ctx->pipe_scratch[0], s);
   if (rc) return rc;
@@ -872,6 +927,7 @@ int voda_place(voda_ctx* ctx, const voda_place_batch* b, const voda_place_out* o
   }
   auto d2h = [&](void* dst, size_t at, size_t bytes) -> cudaError_t {
     if (!bytes || !dst) return cudaSuccess;
+    ctx->d2h_bytes += (int64_t)bytes;
     if (gathered) {
       std::memcpy(dst, hs + at, bytes);
       return cudaSuccess;

@@ -34,8 +34,9 @@ cudaError_t launch_munkres(int n, int batch, const int64_t* A, int32_t* out, int
 
 // bestFit + score + munkres placement rounds (place.cu)
 size_t place_smem_bytes(const PlaceArgs& a);
-size_t place_scratch_bytes(const PlaceArgs& a, int sms);
-cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream, int* launched);
+size_t place_scratch_bytes(const PlaceArgs& a, int sms, int rounds = -1);
+cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream, int* launched, int first = 0,
+                         int last = -1);
 
 // speedup-curve builder (curves.cu)
 cudaError_t launch_curves(int jobs, const int32_t* rec_off, const int32_t* workers, const double* t, int W,

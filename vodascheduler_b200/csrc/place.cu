@@ -490,46 +490,50 @@ static int place_grid(const PlaceArgs& a, int rounds, int sms, size_t smem, cuda
 
 // The split form pays a second launch and a slab per round: it is used for batches of at least a few
 // waves of the fused kernel, without a pod table (the migration counts need the fused kernel's state).
-static bool place_split(const PlaceArgs& a, int sms) {
+static bool place_split(const PlaceArgs& a, int rounds, int sms) {
   if (const char* v = std::getenv("VODA_PLACE_SPLIT")) return std::atoi(v) != 0 && !a.pods_off;
-  return !a.pods_off && a.rounds >= 4 * 10 * sms;
+  return !a.pods_off && rounds >= 2 * 10 * sms;
 }
 // rounds of the split form processed per pair of launches: their slabs may take 2 GiB; equal sub-batches
-static int place_split_rounds(const PlaceArgs& a) {
+static int place_split_rounds(const PlaceArgs& a, int rounds) {
   const size_t per = place_slab_ints(a) * 4;
   const size_t cap = std::max<size_t>(1, ((size_t)2 << 30) / per);
-  const size_t parts = ((size_t)a.rounds + cap - 1) / cap;
-  return (int)(((size_t)a.rounds + parts - 1) / parts);
+  const size_t parts = ((size_t)rounds + cap - 1) / cap;
+  return (int)(((size_t)rounds + parts - 1) / parts);
 }
 
 // bytes of global scratch the launch needs (score-matrix slabs: one per CTA, or one per round of a sub-batch)
-size_t place_scratch_bytes(const PlaceArgs& a, int sms) {
+size_t place_scratch_bytes(const PlaceArgs& a, int sms, int rounds) {
+  if (rounds < 0) rounds = a.rounds;
   const int Mp = next_pow2(a.max_requests > 0 ? a.max_requests : 1);
   // + the rows the last slab's vector loads may touch beyond its matrix (munkres.cuh)
   const size_t slack = (size_t)kMunkresSlackRows * kMaxNodes * 4 + 256;
-  if (place_split(a, sms)) return (size_t)place_split_rounds(a) * place_slab_ints(a) * 4 + slack;
+  if (place_split(a, rounds, sms)) return (size_t)place_split_rounds(a, rounds) * place_slab_ints(a) * 4 + slack;
   const size_t smem = place_smem(Mp);
   if (smem > 48 * 1024) cudaFuncSetAttribute(place_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   cudaError_t e;
-  const int grid = place_grid<false>(a, a.rounds, sms, smem, &e);
+  const int grid = place_grid<false>(a, rounds, sms, smem, &e);
   return (size_t)grid * place_slab_ints(a) * 4 + slack;
 }
 
-// Enqueues the placement of every round; *launched = kernels launched.
-cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream, int* launched) {
+// Enqueues the placement of rounds [first, last) (last < 0: all of them); *launched = kernels launched.
+cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_t stream, int* launched, int first,
+                         int last) {
+  if (last < 0) last = a.rounds;
+  const int rounds = last - first;
   const int Mp = next_pow2(a.max_requests > 0 ? a.max_requests : 1);
   int32_t* slabs = static_cast<int32_t*>(scratch);
   cudaError_t e;
   *launched = 0;
-  if (!place_split(a, sms)) {
+  if (!place_split(a, rounds, sms)) {
     const size_t smem = place_smem(Mp);
     if (smem > 48 * 1024) {
       e = cudaFuncSetAttribute(place_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       if (e != cudaSuccess) return e;
     }
-    const int grid = place_grid<false>(a, a.rounds, sms, smem, &e);
+    const int grid = place_grid<false>(a, rounds, sms, smem, &e);
     if (e != cudaSuccess) return e;
-    place_kernel<false><<<grid, kThreads, smem, stream>>>(a, Mp, slabs, place_slab_ints(a), 0, a.rounds);
+    place_kernel<false><<<grid, kThreads, smem, stream>>>(a, Mp, slabs, place_slab_ints(a), first, last);
     *launched = 1;
     return cudaGetLastError();
   }
@@ -538,9 +542,9 @@ cudaError_t launch_place(const PlaceArgs& a, int sms, void* scratch, cudaStream_
     e = cudaFuncSetAttribute(place_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
   }
-  const int sub = place_split_rounds(a);
-  for (int r0 = 0; r0 < a.rounds; r0 += sub) {
-    const int r1 = std::min(a.rounds, r0 + sub);
+  const int sub = place_split_rounds(a, rounds);
+  for (int r0 = first; r0 < last; r0 += sub) {
+    const int r1 = std::min(last, r0 + sub);
     const int grid = place_grid<true>(a, r1 - r0, sms, smem, &e);
     if (e != cudaSuccess) return e;
     place_kernel<true><<<grid, kThreads, smem, stream>>>(a, Mp, slabs, place_slab_ints(a), r0, r1);
