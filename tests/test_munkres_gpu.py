@@ -67,3 +67,19 @@ def test_rejects_oversize(ctx):
     from vodascheduler_b200 import EngineError
     with pytest.raises(EngineError):
         ctx.munkres_max(np.zeros((1, 129, 129), np.int64))
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 8, 16, 31, 32, 63, 64, 100, 128])
+def test_mixed_sign_scores_wrap_like_the_reference(ctx, oracle, n):
+    """MaxInt64 - score wraps in the reference when a row holds negative and non-negative scores
+    (tests/test_munkres_wrap_cpu.py pins what then comes out); such matrices go to the widest kernel,
+    which computes in the same wrapping arithmetic.  Mixed batches: plain matrices in between."""
+    rng = np.random.default_rng(300 + n)
+    for hi in (1, 8, 255, 999, 70000, 1 << 40):
+        A = synth.matrices(20, n, kind="uniform", hi=hi, seed=500 + n)
+        A[::3] -= int(rng.integers(1, hi + 1))   # every third matrix gets negative entries
+        A[1::6] = -A[1::6] - 1                    # and some are negative throughout
+        got, st = ctx.munkres_max(A)
+        ref, _ = oracle.munkres_max(A, threads=8)
+        assert (st == 0).all()
+        assert np.array_equal(got, ref), (n, hi)

@@ -34,6 +34,14 @@ __device__ __forceinline__ long long warp_max_ll(long long v) {
   return v;
 }
 
+__device__ __forceinline__ long long warp_min_ll(long long v) {
+  for (int d = 16; d > 0; d >>= 1) {
+    long long o = __shfl_xor_sync(0xffffffffu, v, d);
+    v = o < v ? o : v;
+  }
+  return v;
+}
+
 template <typename CellT>
 #ifndef VODA_MK_MINBLOCKS
 #define VODA_MK_MINBLOCKS 32  // 64 registers: all 32 one-warp CTAs of an SM resident (74 registers held 27: 8.1 -> 6.1 ms per 20k matrices)
@@ -104,17 +112,39 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
           mx = __reduce_max_sync(full, mx);
 #pragma unroll
           for (int t = 0; t < 4; t++) c[t] = (Diff)(mx - lo[t]);
+        } else if (sizeof(CellT) == 8) {
+          // The reference forms MaxInt64 - A[i][j] and subtracts the row minimum in wrapping int64
+          // arithmetic (ComputeMunkresMax, then step 1).  For a row of one sign that is rowmax - A; a
+          // row holding negative AND non-negative scores wraps, its cells come out negative or small,
+          // and the assignment the steps then find is still the reference's answer: the widest kernel
+          // computes exactly that, for every row that reaches it.
+          long long ap[4], mn = 0x7fffffffffffffffLL;
+#pragma unroll
+          for (int t = 0; t < 4; t++) {
+            ap[t] = lane + 32 * t < n ? (long long)(0x7fffffffffffffffULL - (unsigned long long)v[q][t]) : 0x7fffffffffffffffLL;
+            mn = ap[t] < mn ? ap[t] : mn;
+          }
+          mn = warp_min_ll(mn);
+#pragma unroll
+          for (int t = 0; t < 4; t++) c[t] = (Diff)((unsigned long long)ap[t] - (unsigned long long)mn);
         } else {
+          bool neg = false, pos = false;
+#pragma unroll
+          for (int t = 0; t < 4; t++) {
+            if (lane + 32 * t < n) {
+              if (v[q][t] < 0) neg = true;
+              else pos = true;
+            }
+          }
+          if (__any_sync(full, neg) && __any_sync(full, pos)) overflow = true;  // mixed signs: the widest kernel's case
           long long mx = v[q][0];
 #pragma unroll
           for (int t = 1; t < 4; t++) mx = v[q][t] > mx ? v[q][t] : mx;
           mx = warp_max_ll(mx);
 #pragma unroll
           for (int t = 0; t < 4; t++) {
-            // rowmax - A: wraps only when the row's range exceeds int64, which no cell type
-            // here can hold either; such a matrix is out of the reference's domain too
-            const unsigned long long d = (unsigned long long)mx - (unsigned long long)v[q][t];
-            c[t] = sizeof(CellT) == 8 ? (Diff)d : (Diff)(d > 0xFFFFFFFFull ? 0xFFFFFFFFull : d);
+            const unsigned long long d = (unsigned long long)mx - (unsigned long long)v[q][t];  // one sign: no wrap
+            c[t] = (Diff)(d > 0xFFFFFFFFull ? 0xFFFFFFFFull : d);
           }
         }
         const uint32_t rowBit = 1u << (i & 31);
@@ -122,7 +152,7 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
         for (int t = 0; t < 4; t++) {
           const int col = lane + 32 * t;
           const bool valid = col < n;
-          if (valid && c[t] > (Diff)CellMax<CellT>::v) overflow = true;
+          if (sizeof(CellT) < 8 && valid && c[t] > (Diff)CellMax<CellT>::v) overflow = true;
           if (valid) C[(size_t)i * n + col] = (CellT)c[t];
           const bool z = valid && c[t] == 0;
           const unsigned bz = __ballot_sync(full, z);
@@ -141,7 +171,7 @@ __global__ void __launch_bounds__(32, VODA_MK_MINBLOCKS) munkres_kernel(int n, i
     if (__any_sync(full, overflow)) {
       if (level < 3) {
         if (lane == 0) need[b] = (unsigned char)(level + 1);  // a wider kernel takes it
-      } else {  // a row's range exceeds int64: outside the reference's domain as well
+      } else {  // (not reached: the widest kernel's arithmetic is the reference's own, wrap included)
         for (int i = lane; i < n; i += 32) out[(size_t)b * n + i] = -1;
         if (lane == 0) status[b] = VODA_ST_BOUND;
       }

@@ -456,21 +456,21 @@ __device__ void munkres_solve(const CellT* __restrict__ C, int n, const MunkresS
         }
       }
     } else {
-      for (int l = 0; l < 32 && 4 * l < n; l++) {
+      // 64-bit potentials serve the widest cells, and those may hold the reference's WRAPPED values
+      // (MaxInt64 - score with mixed signs), negative ones included: then m can be negative and a
+      // covered x covered cell equal to -m becomes a zero as well.  No case analysis here: both masks
+      // are rebuilt from the values, which is what the reference's `== 0` tests see.
+      for (int x = lane; x < 128 * 4; x += 32) sm.zt[x] = 0;
+      __syncwarp();
+      for (int i = 0; i < n; i++) {
+        const Pot rai = ra[i];
+        const CellT* row = C + (size_t)i * n;
 #pragma unroll
-        for (int q = 0; q < 4; q++) {
-          const int i = 4 * l + q;
-          if (i >= n) break;
-          if (mask_test(rowCov, i)) continue;
-          const Pot rai = ra[i];
-          const CellT* row = C + (size_t)i * n;
-#pragma unroll
-          for (int t = 0; t < 4; t++) {
-            const bool z = ucol[t] && ((Pot)row[lane + 32 * t] + rai - cs[t] == 0);
-            const unsigned bz = __ballot_sync(full, z);
-            if (lane == 0 && bz) sm.zr[i * 4 + t] |= bz;
-            if (z) sm.zt[(lane + 32 * t) * 4 + (i >> 5)] |= 1u << (i & 31);
-          }
+        for (int t = 0; t < 4; t++) {
+          const bool z = ucolValid[t] && ((Pot)row[lane + 32 * t] + rai - cs[t] == 0);
+          const unsigned bz = __ballot_sync(full, z);
+          if (lane == 0) sm.zr[i * 4 + t] = bz;
+          if (z) sm.zt[(lane + 32 * t) * 4 + (i >> 5)] |= 1u << (i & 31);
         }
       }
     }
