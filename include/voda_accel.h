@@ -201,7 +201,10 @@ int voda_ffdl_allocate_static(void* stream, const voda_alloc_batch* dev_batch,
  * pkg/placement/placement_manager.go:505-512) for `batch` independent n x n matrices.
  * A is row-major int64, A[b][row*n + col].  out_col_of_row[b][row] is the column of the
  * RowCol{Row,Col} pair whose Row == row (the reference returns pairs in row order).
- * 1 <= n <= 128 (one CTA keeps the whole matrix in shared memory).
+ * 1 <= n <= 128.  Any int64 values: the reference forms MaxInt64 - A[i][j] and subtracts row minima in
+ * Go's wrapping arithmetic, which is the ordinary maximum-weight assignment when every row holds
+ * scores of one sign and something else (still well defined) when a row mixes negative and
+ * non-negative ones; this library computes the reference's answer in both cases.
  */
 int voda_munkres_max(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t* A,
                      int32_t* out_col_of_row /*[batch*n]*/, int32_t* out_status /*[batch]*/);

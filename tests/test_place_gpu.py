@@ -183,3 +183,22 @@ def test_chunked_host_path_equals_single_shot(ctx, oracle):
     rounds = 2 * max(2 * 10 * sms, 1) * 2 + 37  # >= 2 chunks of >= 2 * 10 * sms rounds, not a multiple
     pb = synth.place_batch(rounds=rounds, nodes=12, slots=8, jobs_per_round=20, load=0.9)
     _same(pb, ctx.place(pb), oracle.place(pb, threads=16))
+
+
+@pytest.mark.parametrize("split", ["0", "1"], ids=["fused", "split"])
+@pytest.mark.parametrize("nodes", [3, 4, 16, 37, 64])
+def test_negative_previous_counts_follow_the_reference_wrap(ctx, oracle, monkeypatch, split, nodes):
+    """A previous layout with negative worker counts puts negative scores next to non-negative ones in a
+    row of the score matrix; the reference's MaxInt64 - score then wraps (test_munkres_wrap_cpu.py) and
+    the binding it finds is what the kernel has to find too.  Negative node capacities ride along."""
+    monkeypatch.setenv("VODA_PLACE_SPLIT", split)
+    rng = np.random.default_rng(40 + nodes)
+    for it in range(4):
+        pb = synth.place_batch(rounds=20, nodes=nodes, slots=int(rng.choice([2, 4, 8])), jobs_per_round=nodes + 4,
+                               load=float(rng.choice([0.6, 0.9, 1.1])), seed=900 + 7 * nodes + it)
+        m = rng.random(pb.prev_workers.shape[0]) < 0.15
+        pb.prev_workers = np.where(m, -pb.prev_workers - int(rng.integers(0, 3)), pb.prev_workers).astype(pb.prev_workers.dtype)
+        if it % 2:
+            m = rng.random(pb.node_slots.shape[0]) < 0.1
+            pb.node_slots = np.where(m, -int(rng.integers(0, 3)), pb.node_slots).astype(pb.node_slots.dtype)
+        _same(pb, ctx.place(pb), oracle.place(pb, threads=8))

@@ -58,23 +58,37 @@ __device__ long long place_solve(const PlaceSmem& sm, int n, int lane) {
   __syncwarp();
   bool wide = false;  // some cell of rowmax - M is too large for 32-bit potentials
   uint32_t acc[4] = {0, 0, 0, 0};  // zeros of the current block of 32 rows in columns lane + 32 t
+  // Rows mixing negative and non-negative scores (a previous layout with negative counts): the
+  // reference's MaxInt64 - score wraps there (munkres.cu).  With k = the smallest |score| among the
+  // row's negative ones, what its step 1 leaves is |score| - k for the negative scores and
+  // -(score + k) for the others: in both cases (-k) - score, so rowmax[i] keeps -k for such a row and
+  // the total score is recovered from the cells the same way as for the others.
   for (int i = 0; i < n; i++) {
     int v[4];
-    int mx = (int)0x80000000;
+    int mx = (int)0x80000000, negMax = (int)0x80000000;
 #pragma unroll
     for (int t = 0; t < 4; t++) {
       const int col = lane + 32 * t;
       v[t] = col < n ? sm.M[i * n + col] : (int)0x80000000;
       mx = max(mx, v[t]);
+      if (sizeof(CellT) == 4 && col < n && v[t] < 0) negMax = max(negMax, v[t]);
     }
     mx = __reduce_max_sync(full, mx);
-    if (lane == 0) sm.rowmax[i] = mx;
+    bool mixed = false;
+    int k = 0;
+    if (sizeof(CellT) == 4 && mx >= 0) {  // (a row with a non-negative maximum may also hold negative scores)
+      negMax = __reduce_max_sync(full, negMax);
+      mixed = negMax != (int)0x80000000;
+      k = -negMax;
+    }
+    if (lane == 0) sm.rowmax[i] = mixed ? -k : mx;
     const uint32_t rowBit = 1u << (i & 31);
 #pragma unroll
     for (int t = 0; t < 4; t++) {
       const int col = lane + 32 * t;
       const bool ok = col < n;
-      const int c = ok ? mx - v[t] : 1;
+      int c = ok ? mx - v[t] : 1;
+      if (mixed && ok) c = -k - v[t];  // = |score| - k for a negative score, -(score + k) otherwise
       wide |= ok && (unsigned)c >= (1u << 23);
       if (ok) C[i * n + col] = (CellT)c;
       const bool z = ok && c == 0;
@@ -93,6 +107,7 @@ __device__ long long place_solve(const PlaceSmem& sm, int n, int lane) {
   __syncwarp();
   // the potentials are bounded by n * max cell: 32 bits unless a cell reaches 2^23 (scores are sums
   // of workers on one node: only a degenerate input gets there)
+  // (negative cells count as wide: the 64-bit form of step 6 rebuilds its zero masks from the values)
   if (sizeof(CellT) == 4 && __any_sync(full, wide)) munkres_solve<CellT, int64_t>(C, n, sm.mk);
   else munkres_solve<CellT, int32_t>(C, n, sm.mk);
   long long sc = 0;
@@ -362,9 +377,9 @@ __global__ void __launch_bounds__(kThreads, SPLIT ? 1 : VODA_PLACE_MINBLOCKS)
       }
       const long long span = (long long)hi - (long long)lo;
       long long sc;
-      if (span < 256) sc = place_solve<uint8_t>(sm, n, lane);
-      else if (span < 65536) sc = place_solve<uint16_t>(sm, n, lane);
-      else sc = place_solve<int32_t>(sm, n, lane);
+      if (lo >= 0 && span < 256) sc = place_solve<uint8_t>(sm, n, lane);
+      else if (lo >= 0 && span < 65536) sc = place_solve<uint16_t>(sm, n, lane);
+      else sc = place_solve<int32_t>(sm, n, lane);  // also every matrix with a negative score (signed cells)
       for (int i = lane; i < n; i += 32) a.phys_of_logical[n0 + i] = sm.mk.starCol[i];
       if (lane == 0) {
         a.score[rd] = sc;
@@ -454,9 +469,9 @@ __global__ void __launch_bounds__(32, VODA_SOLVE_MINBLOCKS) place_solve_kernel(P
     hi = __reduce_max_sync(full, hi);
     const long long span = (long long)hi - (long long)lo;
     long long sc;
-    if (span < 256) sc = place_solve<uint8_t>(sm, n, lane);
-    else if (span < 65536) sc = place_solve<uint16_t>(sm, n, lane);
-    else sc = place_solve<int32_t>(sm, n, lane);
+    if (lo >= 0 && span < 256) sc = place_solve<uint8_t>(sm, n, lane);
+    else if (lo >= 0 && span < 65536) sc = place_solve<uint16_t>(sm, n, lane);
+    else sc = place_solve<int32_t>(sm, n, lane);  // also every matrix with a negative score (signed cells)
     for (int i = lane; i < n; i += 32) a.phys_of_logical[n0 + i] = sm.mk.starCol[i];
     if (lane == 0) {
       a.score[rd] = sc;
