@@ -226,6 +226,9 @@ int voda_munkres_max_dev(voda_ctx* ctx, int32_t n, int32_t batch, const int64_t*
  *   prev_workers                 over the flat node index: entries of node i are
  *                                [prev_off[i], prev_off[i+1]), prev_job is a round-local job
  *                                index, prev_workers its jobNumWorkers value on that node.
+ *                                A job appears AT MOST ONCE in a node's list (the reference keeps
+ *                                a Go map per node: repeated keys cannot exist there); the values
+ *                                may be anything, negative ones included.
  *   pods_off / pods_node /       OPTIONAL (all three or none): the pod -> node table the round starts
  *   pods_slots                   from (pm.podNodeName, :571-617), run-length coded per request: the
  *                                runs of request q (flat index req_off[r] + q) are [pods_off[q],
