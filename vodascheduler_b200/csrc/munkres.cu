@@ -10,7 +10,9 @@
 // hardware limit of 32 one-warp CTAs per SM.  The cell type is found by trying: the uint8
 // kernel runs over the whole batch and marks the matrices whose range does not fit; the
 // uint16 / int32 / int64 kernels then pick up only what was marked (each is an almost-empty
-// launch when nothing was).  The solve itself is munkres.cuh.
+// launch when nothing was).  A matrix with a row that mixes negative and non-negative scores goes to
+// the widest kernel whatever its range: the reference's MaxInt64 - score wraps there, and only that
+// kernel computes in the same wrapping arithmetic.  The solve itself is munkres.cuh.
 #include <type_traits>
 
 #include "kernels.h"
